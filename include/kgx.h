@@ -1,0 +1,247 @@
+/*
+ * kgx.h — C ABI of libkgx: the B200-native join → reduce → render path of a
+ * per-pod GPU metrics exporter.
+ *
+ * This is the drop-in boundary for the hot path of the reference exporter
+ * (reference: /root/reference/main.go).  The reference has no FFI of its own:
+ * its hot path is the inline loop main.go:141-154 (join + value calc +
+ * GaugeVec upsert) and the promhttp render behind main.go:69-71.  Each entry
+ * point below names the reference lines it replaces.  A Go host keeps the
+ * NVML polling (main.go:117-138), the pod/PID discovery (main.go:77-114) and
+ * the prometheus.Collector / http.Handler surface, and calls these functions
+ * through cgo.
+ *
+ * Conventions
+ *   - plain C, no C++ types, no exceptions across the boundary;
+ *   - every function returns 0 (KGX_OK) or a negative KGX_E_* code and never
+ *     aborts the process (the reference calls log.Fatalf / panic instead,
+ *     main.go:47,59,79,119);
+ *   - the caller owns every buffer it passes in; the library copies what it
+ *     needs before returning and owns all device memory;
+ *   - one kgx_ctx per GPU, no global state; calls on one ctx are serialised
+ *     by the library (one writer, any number of readers; readers see the
+ *     last completed ingest).
+ *   - there is NO CPU fallback: without a CUDA device kgx_create fails with
+ *     KGX_E_CUDA.
+ */
+#ifndef KGX_H
+#define KGX_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KGX_ABI_VERSION 1
+
+/* ---- error codes -------------------------------------------------------- */
+#define KGX_OK 0
+#define KGX_E_INVAL (-1)   /* bad argument, bad UTF-8 in a label, bad ids     */
+#define KGX_E_NOMEM (-2)   /* host or device allocation failed                */
+#define KGX_E_CUDA (-3)    /* CUDA runtime error; text via kgx_last_error     */
+#define KGX_E_NOSPACE (-4) /* caller's output buffer too small; *len = needed */
+#define KGX_E_STATE (-5)   /* call order (e.g. ingest before set_table)       */
+#define KGX_E_LIMIT (-6)   /* size beyond a documented maximum                */
+
+/* ---- result modes (SURVEY.md section 8 "Modes") ---------------------------
+ * R modes reproduce main.go exactly: families and help strings of
+ * main.go:22-35, labels pid,pod, values of main.go:147,149, last write wins
+ * in sample order, series persist forever (no Delete/Reset in main.go).
+ *   KGX_MODE_R_INTENDED  join predicate "PID value equality" (what
+ *                        main.go:144-145 means to do)
+ *   KGX_MODE_R_LITERAL   join predicate exactly as written at main.go:144-145:
+ *                        `for pid := range pids` yields slice INDICES, so a
+ *                        process matches pod P iff Pid < len(pids of P) and
+ *                        the pid label is that index.
+ * X mode is the north-star extension (not in the reference): key
+ * (pod, namespace, container, gpu); integer sum / max / last-timestamp /
+ * count reductions over a window of ingests.
+ */
+#define KGX_MODE_R_INTENDED 0
+#define KGX_MODE_R_LITERAL 1
+#define KGX_MODE_X 2
+
+typedef struct kgx_ctx kgx_ctx;
+
+typedef struct kgx_opts {
+  int32_t abi_version;   /* must be KGX_ABI_VERSION                           */
+  int32_t mode;          /* KGX_MODE_*                                        */
+  void* stream;          /* cudaStream_t to run on, or NULL: library-owned    */
+  int32_t profile;       /* 1: record per-kernel CUDA-event times             */
+  int32_t reserved;
+} kgx_opts;
+
+/* The join table: the device-side form of `podPIDMap map[string][]string`
+ * (main.go:84,109,113), widened by node id and, in X mode, namespace and
+ * container.  A "podkey" is one map key: the pod name in R modes
+ * (main.go:113 keys by name only), (pod, namespace, container) in X mode.
+ * Entries are the PID lists flattened: entry i says "pid entry_pid[i] is in
+ * the list of podkey entry_podkey[i]"; duplicates are allowed, as the
+ * reference appends one `ps` output per container (main.go:109).  Strings are
+ * raw (unescaped) UTF-8, given as one blob plus n+1 byte offsets.
+ */
+typedef struct kgx_table {
+  uint32_t n_nodes;        /* >= 1; node ids are 0..n_nodes-1                  */
+  uint32_t gpus_per_node;  /* G >= 1; gpu ids are 0..G-1 within a node         */
+  uint64_t n_podkeys;
+  const uint32_t* podkey_node;   /* [n_podkeys]                                */
+  const char* pod_blob;
+  const uint64_t* pod_off;       /* [n_podkeys+1]                              */
+  const char* namespace_blob;    /* X mode only, else NULL                     */
+  const uint64_t* namespace_off; /* [n_podkeys+1]                              */
+  const char* container_blob;    /* X mode only, else NULL                     */
+  const uint64_t* container_off; /* [n_podkeys+1]                              */
+  uint64_t n_entries;
+  const uint32_t* entry_podkey;  /* [n_entries]                                */
+  const uint32_t* entry_pid;     /* [n_entries]                                */
+  const char* gpu_uuid_blob;     /* X mode only: value of the gpu label        */
+  const uint64_t* gpu_uuid_off;  /* [n_nodes*G+1], index node*G+gpu            */
+} kgx_table;
+
+/* One batch of per-process samples in column form: what main.go:123-138 reads
+ * from NVML each cycle (nvml.h nvmlProcessInfo_t: pid, usedGpuMemory;
+ * nvmlMemory_t: total), in the loop order of main.go:123,141 (device index
+ * ascending, then process order) — in R modes the LAST sample in this order
+ * wins for a series, as repeated GaugeVec.Set does.  X mode adds the
+ * utilisation and timestamp columns (nvml.h nvmlProcessUtilizationSample_t).
+ * All pointers are host memory (pageable or from kgx_host_alloc).
+ */
+typedef struct kgx_cols {
+  uint64_t n;
+  const uint32_t* pid;       /* [n]                                            */
+  const uint32_t* gpu;       /* [n] device index within the node               */
+  const uint64_t* used;      /* [n] usedGpuMemory bytes                        */
+  const uint32_t* node;      /* [n] or NULL (= all node 0)                     */
+  const uint32_t* sm_util;   /* [n] X mode                                     */
+  const uint32_t* mem_util;  /* [n] X mode                                     */
+  const uint64_t* ts_us;     /* [n] X mode                                     */
+  const uint64_t* node_off;  /* optional [n_nodes+1]: samples of node k are
+                                rows node_off[k]..node_off[k+1]; lets the join
+                                stage each node's table slice in shared memory */
+  const uint64_t* gpu_total; /* [n_nodes*G] memoryInfo.Total, main.go:129,149  */
+} kgx_cols;
+
+typedef struct kgx_stats {
+  uint64_t n_series;        /* series with a value after the last ingest       */
+  uint64_t n_slots;         /* potential series the table can produce          */
+  uint64_t n_matched;       /* samples of the last ingest that joined          */
+  uint64_t n_dropped;       /* samples of the last ingest with no table entry  */
+  uint64_t rendered_bytes;  /* size of the last rendered body                  */
+  uint64_t kernel_launches; /* kernels launched by this ctx so far             */
+  uint64_t rebuilds;        /* series-index rebuilds (churn) so far            */
+  uint64_t device_bytes;    /* device memory currently held                    */
+} kgx_stats;
+
+/* Per-kernel device times (opts.profile = 1), accumulated since the last
+ * kgx_profile_reset.  Index with KGX_K_*. */
+#define KGX_K_INGEST 0   /* join + reduce                                      */
+#define KGX_K_FINALIZE 1 /* R modes: fetch values of last-writer samples       */
+#define KGX_K_INDEX 2    /* series-index rebuild kernels (churn only)          */
+#define KGX_K_RENDER 3   /* exposition writer                                  */
+#define KGX_K_OTHER 4    /* clears, tile bookkeeping                           */
+#define KGX_K_COUNT 5
+typedef struct kgx_profile {
+  double ms[KGX_K_COUNT];
+  uint64_t launches[KGX_K_COUNT];
+} kgx_profile;
+
+/* ---- lifecycle ---------------------------------------------------------- */
+
+/* Create a context on CUDA device `device`.
+ * Replaces: the registry + two GaugeVecs of main.go:21-36,40-42 (the schema
+ * is fixed by `mode`). */
+int kgx_create(int device, const kgx_opts* opts, kgx_ctx** out);
+void kgx_destroy(kgx_ctx* ctx);
+
+/* ---- cold path ---------------------------------------------------------- */
+
+/* Install the join table (podPIDMap of main.go:84-114).  Builds, on the host,
+ * the output order of every series the table can produce (Registry.Gather's
+ * sort, see DESIGN.md "Order"), the pre-escaped label bytes and the
+ * open-addressing hash table, and uploads them.
+ * R modes: series already exported keep their last value across calls, as
+ * GaugeVec children do (main.go has no Delete/Reset).  X mode: clears the
+ * window. */
+int kgx_set_table(kgx_ctx* ctx, const kgx_table* table);
+
+/* ---- hot path ----------------------------------------------------------- */
+
+/* Join one batch of samples to the table and fold it into the per-series
+ * state.  Replaces the loop at main.go:141-154 (join :141-145, values
+ * :147,149, upsert :147,150). */
+int kgx_ingest(kgx_ctx* ctx, const kgx_cols* cols);
+
+/* Same, with every column pointer being DEVICE memory already resident on
+ * ctx's GPU (no host<->device copy).  Used to time the device pipeline. */
+int kgx_ingest_device(kgx_ctx* ctx, const kgx_cols* cols);
+
+/* X mode: start a new aggregation window (forget sums/max/last/count).
+ * No-op error KGX_E_STATE in R modes, whose series never reset. */
+int kgx_reset_window(kgx_ctx* ctx);
+
+/* Render the Prometheus text exposition (format 0.0.4) of the current state
+ * into ctx-owned device memory.  Replaces what promhttp.HandlerFor serves at
+ * main.go:69-71 (Registry.Gather + expfmt text encoder).  One body per node,
+ * concatenated in node order.  *len receives the total size. */
+int kgx_render_device(kgx_ctx* ctx, size_t* len);
+
+/* Render (as above) and copy the bytes to host memory `out` of capacity
+ * `cap`.  If cap is too small returns KGX_E_NOSPACE with *len = needed. */
+int kgx_render(kgx_ctx* ctx, uint8_t* out, size_t cap, size_t* len);
+
+/* Device pointer and size of the last rendered text (valid until the next
+ * render on this ctx); for peer copies / NCCL gathers of bodies. */
+int kgx_body_device(kgx_ctx* ctx, const uint8_t** dptr, size_t* len);
+
+/* Byte offset of every node's body inside the last rendered text:
+ * off[k]..off[k+1] is node k's /metrics body; off has n_nodes+1 entries. */
+int kgx_body_offsets(kgx_ctx* ctx, uint64_t* off, size_t n);
+
+/* ---- Collector read-back (prometheus.Collector.Collect) ------------------ */
+
+/* Values of family `family` (index in sorted family order) for every series
+ * that has a value, in exposition order; *n receives the count.  With
+ * slots != NULL also returns each series' slot id, resolvable to label values
+ * with kgx_slot_labels.  Replaces GaugeVec.Collect reached from main.go:41-42. */
+int kgx_read_values(kgx_ctx* ctx, int family, double* values, uint32_t* slots,
+                    size_t cap, size_t* n);
+int kgx_family_count(kgx_ctx* ctx);
+/* name/help/label names of a family; pointers valid for ctx's lifetime. */
+int kgx_family_info(kgx_ctx* ctx, int family, const char** name,
+                    const char** help, const char* const** label_names,
+                    int* n_labels);
+/* The pre-escaped label text `{a="..",b=".."}` of a slot; copies at most cap
+ * bytes, *len = full length. */
+int kgx_slot_labels(kgx_ctx* ctx, uint32_t slot, char* out, size_t cap,
+                    size_t* len);
+
+/* ---- utilities ---------------------------------------------------------- */
+
+/* Format n doubles on the GPU exactly as expfmt writes sample values
+ * (strconv.AppendFloat(f,'g',-1,64) plus the 0/1/-1/NaN/Inf special cases),
+ * one value per 32-byte record: bytes 0..23 text, byte 31 length.  Test and
+ * diagnostic entry point for the device float printer. */
+int kgx_format_values(kgx_ctx* ctx, const double* values, size_t n,
+                      uint8_t* out32);
+
+/* Pinned host memory for sample columns and output (faster PCIe copies). */
+void* kgx_host_alloc(size_t bytes);
+void kgx_host_free(void* p);
+
+int kgx_get_stats(kgx_ctx* ctx, kgx_stats* out);
+int kgx_get_profile(kgx_ctx* ctx, kgx_profile* out);
+int kgx_profile_reset(kgx_ctx* ctx);
+/* Block until all work queued by this ctx has finished. */
+int kgx_sync(kgx_ctx* ctx);
+
+const char* kgx_strerror(int code);
+/* Detail of the last error on ctx (valid until the next call on ctx). */
+const char* kgx_last_error(kgx_ctx* ctx);
+int kgx_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KGX_H */
