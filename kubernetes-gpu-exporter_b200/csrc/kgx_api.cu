@@ -1,0 +1,763 @@
+// kgx_api.cu — the C ABI of include/kgx.h: context, device memory, and the
+// launch sequences of the join -> reduce -> render path.  No CPU fallback: every
+// entry point that computes needs the CUDA device the ctx was created on.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/kgx.h"
+#include "kgx_kernels.cuh"
+#include "kgx_table.hpp"
+
+using namespace kgx;
+
+namespace {
+
+struct DBuf {  // growable device buffer
+  void* p = nullptr;
+  size_t cap = 0;
+};
+
+struct TimedRegion { int kind; cudaEvent_t a, b; };
+
+}  // namespace
+
+struct kgx_ctx {
+  int device = 0, mode = 0;
+  bool profile = false, own_stream = false;
+  cudaStream_t stream = nullptr;
+  std::mutex mu;
+  std::string err;
+  int sm_count = 148;
+  size_t device_bytes = 0;
+
+  bool have_table = false;
+  Plan plan;
+  // table
+  DBuf d_node_tab, d_tab, d_pk_slot0, d_pk_stride, d_grank, d_node_slot_base;
+  DBuf d_A_blob, d_B_blob, d_G_blob, d_A_off, d_B_off, d_G_off, d_runs;
+  // index
+  DBuf d_bm, d_pending, d_popc, d_prefix, d_block_sums;
+  uint32_t n_words = 0;
+  // series
+  uint32_t n_series = 0;
+  DBuf d_ser_slot, d_ser_a, d_ser_gidx, d_ser_len, d_lbl_off, d_lbl_blob, d_node_ser_off;
+  uint64_t lbl_bytes = 0;
+  std::vector<uint32_t> node_ser_off;
+  // per-series state
+  DBuf d_acc[6];  // X: sum_used,max_used,last_ts,sum_sm,sum_mem,count ; R: r_seq,r_used,r_total
+  DBuf d_node_live, d_gpu_total;
+  bool have_total = false;
+  // render
+  DBuf d_fam, d_tiles, d_tile_state, d_node_body_off, d_out;
+  uint32_t n_tiles = 0, tile_lines = 0, render_smem = 0;
+  int render_grid = 0;
+  size_t last_len = 0;
+  bool rendered = false;
+  std::vector<FamMeta> fam;
+  // misc
+  DBuf d_counters;
+  unsigned long long* h_counters = nullptr;  // pinned
+  DBuf d_cols[8];
+  DBuf d_tmp[4];
+  uint32_t seq = 0;
+  kgx_stats stats{};
+  kgx_profile prof{};
+  std::vector<TimedRegion> regions;
+};
+
+namespace {
+
+const char* const kErrNames[] = {"ok", "invalid argument", "out of memory", "CUDA error", "output buffer too small",
+                                 "call out of order", "size beyond a documented maximum"};
+
+#define KGX_CUDA(c, call)                                                                      \
+  do {                                                                                         \
+    cudaError_t e_ = (call);                                                                   \
+    if (e_ != cudaSuccess) {                                                                   \
+      (c)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                           \
+      return e_ == cudaErrorMemoryAllocation ? KGX_E_NOMEM : KGX_E_CUDA;                       \
+    }                                                                                          \
+  } while (0)
+
+#define KGX_TRY(expr)         \
+  do {                        \
+    int rc_ = (expr);         \
+    if (rc_ != KGX_OK) return rc_; \
+  } while (0)
+
+int fail(kgx_ctx* c, int code, const char* msg) { c->err = msg; return code; }
+
+int dev_reserve(kgx_ctx* c, DBuf& b, size_t bytes) {
+  if (bytes <= b.cap && b.p) return KGX_OK;
+  if (b.p) { cudaFree(b.p); c->device_bytes -= b.cap; b.p = nullptr; b.cap = 0; }
+  size_t want = std::max<size_t>(bytes, 256);
+  KGX_CUDA(c, cudaMalloc(&b.p, want));
+  b.cap = want;
+  c->device_bytes += want;
+  return KGX_OK;
+}
+void dev_free(kgx_ctx* c, DBuf& b) {
+  if (b.p) { cudaFree(b.p); c->device_bytes -= b.cap; }
+  b.p = nullptr; b.cap = 0;
+}
+template <class T>
+int upload(kgx_ctx* c, DBuf& b, const T* src, size_t n) {
+  KGX_TRY(dev_reserve(c, b, n * sizeof(T)));
+  if (n) KGX_CUDA(c, cudaMemcpyAsync(b.p, src, n * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+  return KGX_OK;
+}
+template <class T> T* ptr(const DBuf& b) { return static_cast<T*>(b.p); }
+
+struct Timed {  // CUDA-event bracket around a launch sequence when profiling
+  kgx_ctx* c; int kind; cudaEvent_t a = nullptr, b = nullptr;
+  Timed(kgx_ctx* c_, int kind_) : c(c_), kind(kind_) {
+    if (!c->profile) return;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    cudaEventRecord(a, c->stream);
+  }
+  void launches(int n) { c->stats.kernel_launches += n; c->prof.launches[kind] += n; }
+  ~Timed() {
+    if (!c->profile) return;
+    cudaEventRecord(b, c->stream);
+    c->regions.push_back(TimedRegion{kind, a, b});
+  }
+};
+
+int launch_check(kgx_ctx* c, const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { c->err = std::string(what) + ": " + cudaGetErrorString(e); return KGX_E_CUDA; }
+  return KGX_OK;
+}
+
+inline uint32_t cdiv(uint64_t a, uint64_t b) { return uint32_t((a + b - 1) / b); }
+
+// exclusive scan of n u32 items -> out64 and/or out32; total -> *total_host (sync)
+int device_scan(kgx_ctx* c, const uint32_t* in, uint64_t n, unsigned long long* out64, uint32_t* out32,
+                unsigned long long* total_host) {
+  const uint32_t nb = std::max<uint32_t>(1, cdiv(n, kScanBlock * kScanItems));
+  KGX_TRY(dev_reserve(c, c->d_block_sums, (size_t(nb) + 1) * 8));
+  unsigned long long* bs = ptr<unsigned long long>(c->d_block_sums);
+  k_scan_reduce<<<nb, kScanBlock, 0, c->stream>>>(in, n, bs);
+  k_scan_blocksums<<<1, 1024, 0, c->stream>>>(bs, nb, bs + nb);
+  k_scan_apply<<<nb, kScanBlock, 0, c->stream>>>(in, n, bs, out64, out32);
+  KGX_TRY(launch_check(c, "scan"));
+  KGX_CUDA(c, cudaMemcpyAsync(total_host, bs + nb, 8, cudaMemcpyDeviceToHost, c->stream));
+  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  return KGX_OK;
+}
+
+DevAcc acc_view(kgx_ctx* c) {
+  DevAcc a{};
+  if (c->mode == KGX_MODE_X) {
+    a.sum_used = ptr<unsigned long long>(c->d_acc[0]); a.max_used = ptr<unsigned long long>(c->d_acc[1]);
+    a.last_ts = ptr<unsigned long long>(c->d_acc[2]); a.sum_sm = ptr<unsigned long long>(c->d_acc[3]);
+    a.sum_mem = ptr<unsigned long long>(c->d_acc[4]); a.count = ptr<unsigned long long>(c->d_acc[5]);
+  } else {
+    a.r_seq = ptr<unsigned long long>(c->d_acc[0]); a.r_used = ptr<unsigned long long>(c->d_acc[1]);
+    a.r_total = ptr<unsigned long long>(c->d_acc[2]);
+  }
+  a.node_live = ptr<uint32_t>(c->d_node_live);
+  return a;
+}
+int n_acc_arrays(const kgx_ctx* c) { return c->mode == KGX_MODE_X ? 6 : 3; }
+
+DevLabels labels_view(kgx_ctx* c) {
+  DevLabels L{};
+  L.A_blob = ptr<uint8_t>(c->d_A_blob); L.B_blob = ptr<uint8_t>(c->d_B_blob); L.G_blob = ptr<uint8_t>(c->d_G_blob);
+  L.A_off = ptr<unsigned long long>(c->d_A_off); L.B_off = ptr<unsigned long long>(c->d_B_off);
+  L.G_off = ptr<unsigned long long>(c->d_G_off);
+  L.runs = ptr<Run>(c->d_runs); L.n_runs = uint32_t(c->plan.runs.size());
+  return L;
+}
+
+void build_family_meta(kgx_ctx* c) {
+  c->fam.clear();
+  for (const FamilyDef& f : families(c->mode)) {
+    FamMeta m{};
+    m.name_len = uint32_t(strlen(f.name));
+    memcpy(m.name, f.name, m.name_len);
+    std::string h = std::string("# HELP ") + f.name + " ";
+    for (const char* p = f.help; *p; ++p) {  // expfmt escapes \ and newline in help (G2)
+      if (*p == '\\') h += "\\\\"; else if (*p == '\n') h += "\\n"; else h += *p;
+    }
+    h += std::string("\n# TYPE ") + f.name + " gauge\n";
+    m.header_len = uint32_t(h.size());
+    memcpy(m.header, h.data(), h.size());
+    m.kind = f.value_kind;
+    c->fam.push_back(m);
+  }
+}
+
+// Merge the pending slots into the series index, re-rank every series, move
+// the per-series state to the new ranks, re-materialise label text and tiles.
+int rebuild_index(kgx_ctx* c) {
+  Timed tm(c, KGX_K_INDEX);
+  const uint32_t nw = c->n_words;
+  const uint32_t old_n = c->n_series;
+  KGX_TRY(dev_reserve(c, c->d_popc, size_t(nw) * 4));
+  KGX_TRY(dev_reserve(c, c->d_prefix, size_t(nw) * 4));
+  k_merge_pending<<<cdiv(nw, 256), 256, 0, c->stream>>>(ptr<uint2>(c->d_bm), ptr<uint32_t>(c->d_pending), nw,
+                                                        ptr<uint32_t>(c->d_popc));
+  unsigned long long total = 0;
+  KGX_TRY(device_scan(c, ptr<uint32_t>(c->d_popc), nw, nullptr, ptr<uint32_t>(c->d_prefix), &total));
+  k_set_prefix<<<cdiv(nw, 256), 256, 0, c->stream>>>(ptr<uint2>(c->d_bm), ptr<uint32_t>(c->d_prefix), nw);
+  tm.launches(5);
+  const uint32_t S = uint32_t(total);
+  // new per-series state, zeroed, then the old state moved over
+  const int na = n_acc_arrays(c);
+  DBuf new_acc[6];
+  for (int k = 0; k < na; ++k) {
+    KGX_TRY(dev_reserve(c, new_acc[k], size_t(S) * 8));
+    KGX_CUDA(c, cudaMemsetAsync(new_acc[k].p, 0, size_t(S) * 8, c->stream));
+  }
+  if (old_n) {
+    const unsigned long long* h_old[6]; unsigned long long* h_new[6];
+    for (int k = 0; k < na; ++k) { h_old[k] = ptr<unsigned long long>(c->d_acc[k]); h_new[k] = ptr<unsigned long long>(new_acc[k]); }
+    KGX_TRY(dev_reserve(c, c->d_tmp[0], 2 * 6 * sizeof(void*)));
+    KGX_CUDA(c, cudaMemcpyAsync(c->d_tmp[0].p, h_old, sizeof h_old, cudaMemcpyHostToDevice, c->stream));
+    KGX_CUDA(c, cudaMemcpyAsync(static_cast<char*>(c->d_tmp[0].p) + sizeof h_old, h_new, sizeof h_new, cudaMemcpyHostToDevice, c->stream));
+    k_remap<<<cdiv(old_n, 256), 256, 0, c->stream>>>(ptr<uint32_t>(c->d_ser_slot), old_n, ptr<uint2>(c->d_bm), na,
+                                                     reinterpret_cast<const unsigned long long* const*>(c->d_tmp[0].p),
+                                                     reinterpret_cast<unsigned long long* const*>(static_cast<char*>(c->d_tmp[0].p) + sizeof h_old));
+    tm.launches(1);
+    KGX_CUDA(c, cudaStreamSynchronize(c->stream));  // h_old/h_new are stack arrays
+  }
+  for (int k = 0; k < na; ++k) { dev_free(c, c->d_acc[k]); c->d_acc[k] = new_acc[k]; }
+  // series arrays
+  KGX_TRY(dev_reserve(c, c->d_ser_slot, size_t(S) * 4));
+  KGX_TRY(dev_reserve(c, c->d_ser_a, size_t(S) * 4));
+  KGX_TRY(dev_reserve(c, c->d_ser_gidx, size_t(S) * 4));
+  KGX_TRY(dev_reserve(c, c->d_ser_len, size_t(S) * 4 + 4));
+  KGX_TRY(dev_reserve(c, c->d_lbl_off, (size_t(S) + 1) * 8));
+  DevLabels L = labels_view(c);
+  k_build_series<<<cdiv(nw, 128), 128, 0, c->stream>>>(ptr<uint2>(c->d_bm), nw, L, ptr<uint32_t>(c->d_ser_slot),
+                                                       ptr<uint32_t>(c->d_ser_a), ptr<uint32_t>(c->d_ser_gidx),
+                                                       ptr<uint32_t>(c->d_ser_len));
+  unsigned long long lbl_total = 0;
+  KGX_TRY(device_scan(c, ptr<uint32_t>(c->d_ser_len), S, ptr<unsigned long long>(c->d_lbl_off), nullptr, &lbl_total));
+  KGX_CUDA(c, cudaMemcpyAsync(ptr<unsigned long long>(c->d_lbl_off) + S, &lbl_total, 8, cudaMemcpyHostToDevice, c->stream));
+  KGX_TRY(dev_reserve(c, c->d_lbl_blob, size_t(lbl_total) + 64));
+  if (S) k_fill_labels<<<cdiv(uint64_t(S) * 32, 256), 256, 0, c->stream>>>(L, ptr<uint32_t>(c->d_ser_a), ptr<uint32_t>(c->d_ser_gidx),
+                                                                           ptr<unsigned long long>(c->d_lbl_off), S,
+                                                                           ptr<uint8_t>(c->d_lbl_blob));
+  // per-node series ranges -> tiles
+  const uint32_t NN = c->plan.n_nodes;
+  KGX_TRY(dev_reserve(c, c->d_node_ser_off, (size_t(NN) + 1) * 4));
+  k_node_ranks<<<cdiv(NN + 1, 256), 256, 0, c->stream>>>(ptr<uint2>(c->d_bm), ptr<uint32_t>(c->d_node_slot_base), NN,
+                                                         uint32_t(c->plan.n_slots), S, ptr<uint32_t>(c->d_node_ser_off));
+  tm.launches(6);
+  KGX_TRY(launch_check(c, "index rebuild"));
+  c->node_ser_off.assign(size_t(NN) + 1, 0);
+  KGX_CUDA(c, cudaMemcpyAsync(c->node_ser_off.data(), c->d_node_ser_off.p, (size_t(NN) + 1) * 4, cudaMemcpyDeviceToHost, c->stream));
+  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->n_series = S;
+  c->lbl_bytes = lbl_total;
+  // tiles: (node, family, chunk of series) in output order
+  std::vector<Tile> tiles;
+  const uint32_t TL = c->tile_lines;
+  const int nf = int(c->fam.size());
+  for (uint32_t n = 0; n < NN; ++n) {
+    const uint32_t lo = c->node_ser_off[n], hi = c->node_ser_off[n + 1];
+    if (hi == lo) continue;
+    for (int f = 0; f < nf; ++f)
+      for (uint32_t k = lo; k < hi; k += TL) {
+        Tile t{};
+        t.first = k; t.node = n; t.count = uint16_t(std::min(TL, hi - k)); t.family = uint8_t(f);
+        t.flags = uint8_t((k == lo ? 1 : 0) | ((k == lo && f == 0) ? 2 : 0));
+        tiles.push_back(t);
+      }
+  }
+  c->n_tiles = uint32_t(tiles.size());
+  KGX_TRY(upload(c, c->d_tiles, tiles.data(), tiles.size()));
+  KGX_TRY(dev_reserve(c, c->d_tile_state, size_t(c->n_tiles) * 8 + 8));
+  // R modes: every series has a value, so a node is live iff it has series
+  if (c->mode != KGX_MODE_X) {
+    std::vector<uint32_t> live(NN);
+    for (uint32_t n = 0; n < NN; ++n) live[n] = c->node_ser_off[n + 1] - c->node_ser_off[n];
+    KGX_CUDA(c, cudaMemcpyAsync(c->d_node_live.p, live.data(), size_t(NN) * 4, cudaMemcpyHostToDevice, c->stream));
+  }
+  // output capacity: an upper bound of the body size
+  uint64_t cap = 64;
+  for (const FamMeta& m : c->fam)
+    cap += uint64_t(S) * (m.name_len + 2 + kMaxValueText) + lbl_total + uint64_t(NN) * m.header_len;
+  KGX_TRY(dev_reserve(c, c->d_out, size_t(cap)));
+  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->stats.rebuilds += 1;
+  return KGX_OK;
+}
+
+void free_table_state(kgx_ctx* c) {
+  DBuf* all[] = {&c->d_node_tab, &c->d_tab, &c->d_pk_slot0, &c->d_pk_stride, &c->d_grank, &c->d_node_slot_base,
+                 &c->d_A_blob, &c->d_B_blob, &c->d_G_blob, &c->d_A_off, &c->d_B_off, &c->d_G_off, &c->d_runs,
+                 &c->d_bm, &c->d_pending, &c->d_popc, &c->d_prefix, &c->d_ser_slot, &c->d_ser_a, &c->d_ser_gidx,
+                 &c->d_ser_len, &c->d_lbl_off, &c->d_lbl_blob, &c->d_node_ser_off, &c->d_node_live, &c->d_gpu_total,
+                 &c->d_tiles, &c->d_tile_state, &c->d_node_body_off, &c->d_out};
+  for (DBuf* b : all) dev_free(c, *b);
+  for (auto& b : c->d_acc) dev_free(c, b);
+  c->n_series = 0; c->n_tiles = 0; c->n_words = 0; c->lbl_bytes = 0; c->have_total = false; c->rendered = false;
+  c->last_len = 0;
+}
+
+int collect_carried(kgx_ctx* c, std::vector<Carried>* out) {
+  out->clear();
+  if (c->mode == KGX_MODE_X || !c->have_table || c->n_series == 0) return KGX_OK;
+  const uint32_t S = c->n_series;
+  std::vector<uint32_t> slot(S);
+  std::vector<unsigned long long> seq(S), used(S), total(S);
+  KGX_CUDA(c, cudaMemcpyAsync(slot.data(), c->d_ser_slot.p, size_t(S) * 4, cudaMemcpyDeviceToHost, c->stream));
+  KGX_CUDA(c, cudaMemcpyAsync(seq.data(), c->d_acc[0].p, size_t(S) * 8, cudaMemcpyDeviceToHost, c->stream));
+  KGX_CUDA(c, cudaMemcpyAsync(used.data(), c->d_acc[1].p, size_t(S) * 8, cudaMemcpyDeviceToHost, c->stream));
+  KGX_CUDA(c, cudaMemcpyAsync(total.data(), c->d_acc[2].p, size_t(S) * 8, cudaMemcpyDeviceToHost, c->stream));
+  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  out->reserve(S);
+  for (uint32_t r = 0; r < S; ++r) {
+    if (!seq[r]) continue;
+    const uint32_t s = slot[r], pod = c->plan.slot_pod[s];
+    out->push_back(Carried{c->plan.pod_node[pod], c->plan.slot_pid[s], c->plan.pod_names[pod], used[r], total[r]});
+  }
+  return KGX_OK;
+}
+
+int upload_plan(kgx_ctx* c) {
+  Plan& p = c->plan;
+  KGX_TRY(upload(c, c->d_node_tab, p.node_tab.data(), p.node_tab.size()));
+  KGX_TRY(upload(c, c->d_tab, p.tab.data(), p.tab.size()));
+  KGX_TRY(upload(c, c->d_pk_slot0, p.pk_slot0.data(), p.pk_slot0.size()));
+  KGX_TRY(upload(c, c->d_pk_stride, p.pk_stride.data(), p.pk_stride.size()));
+  KGX_TRY(upload(c, c->d_grank, p.grank.data(), p.grank.size()));
+  KGX_TRY(upload(c, c->d_node_slot_base, p.node_slot_base.data(), p.node_slot_base.size()));
+  KGX_TRY(upload(c, c->d_A_blob, p.A_blob.data(), p.A_blob.size()));
+  KGX_TRY(upload(c, c->d_B_blob, p.B_blob.data(), p.B_blob.size()));
+  KGX_TRY(upload(c, c->d_G_blob, p.G_blob.data(), p.G_blob.size()));
+  KGX_TRY(upload(c, c->d_A_off, p.A_off.data(), p.A_off.size()));
+  KGX_TRY(upload(c, c->d_B_off, p.B_off.data(), p.B_off.size()));
+  KGX_TRY(upload(c, c->d_G_off, p.G_off.data(), p.G_off.size()));
+  KGX_TRY(upload(c, c->d_runs, p.runs.data(), p.runs.size()));
+  c->n_words = cdiv(p.n_slots, 32) + 1;
+  KGX_TRY(dev_reserve(c, c->d_bm, size_t(c->n_words) * 8));
+  KGX_TRY(dev_reserve(c, c->d_pending, size_t(c->n_words) * 4));
+  KGX_CUDA(c, cudaMemsetAsync(c->d_bm.p, 0, size_t(c->n_words) * 8, c->stream));
+  KGX_CUDA(c, cudaMemsetAsync(c->d_pending.p, 0, size_t(c->n_words) * 4, c->stream));
+  KGX_TRY(dev_reserve(c, c->d_node_live, size_t(p.n_nodes) * 4));
+  KGX_CUDA(c, cudaMemsetAsync(c->d_node_live.p, 0, size_t(p.n_nodes) * 4, c->stream));
+  KGX_TRY(dev_reserve(c, c->d_gpu_total, size_t(p.n_nodes) * p.G * 8));
+  KGX_CUDA(c, cudaMemsetAsync(c->d_gpu_total.p, 0, size_t(p.n_nodes) * p.G * 8, c->stream));
+  KGX_TRY(dev_reserve(c, c->d_node_body_off, (size_t(p.n_nodes) + 1) * 8));
+  KGX_TRY(upload(c, c->d_fam, c->fam.data(), c->fam.size()));
+  // tile geometry: lines per tile so that a whole tile fits the smem buffer
+  uint32_t max_name = 0, max_header = 0;
+  for (const FamMeta& m : c->fam) { max_name = std::max(max_name, m.name_len); max_header = std::max(max_header, m.header_len); }
+  const uint64_t max_line = uint64_t(max_name) + p.max_label_len + 2 + kMaxValueText;
+  const uint64_t budget = 96 * 1024;
+  if (max_line + max_header + 32 > budget) return fail(c, KGX_E_LIMIT, "label text too long for one render tile");
+  c->tile_lines = uint32_t(std::min<uint64_t>(kRenderThreads, (budget - max_header - 32) / max_line));
+  c->render_smem = uint32_t((max_header + uint64_t(c->tile_lines) * max_line + 32 + 15) & ~15ull);
+  KGX_CUDA(c, cudaFuncSetAttribute(k_render, cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->render_smem)));
+  int occ = 1;
+  KGX_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_render, kRenderThreads, c->render_smem));
+  c->render_grid = std::max(1, occ) * c->sm_count;
+  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  return KGX_OK;
+}
+
+int ingest_device_locked(kgx_ctx* c, const kgx_cols* s) {
+  if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_ingest before kgx_set_table");
+  if (!s->gpu_total) return fail(c, KGX_E_INVAL, "cols: gpu_total missing");
+  if (s->n && (!s->pid || !s->gpu || !s->used)) return fail(c, KGX_E_INVAL, "cols: pid/gpu/used missing");
+  const bool x = c->mode == KGX_MODE_X;
+  if (x && s->n && (!s->sm_util || !s->mem_util || !s->ts_us)) return fail(c, KGX_E_INVAL, "cols: X mode needs sm_util, mem_util, ts_us");
+  if (s->n >= 0xffffffffull) return fail(c, KGX_E_LIMIT, "more than 2^32-1 samples in one ingest");
+  const Plan& p = c->plan;
+  KGX_CUDA(c, cudaMemcpyAsync(c->d_gpu_total.p, s->gpu_total, size_t(p.n_nodes) * p.G * 8, cudaMemcpyDefault, c->stream));
+  c->have_total = true;
+  c->seq += 1;
+  c->rendered = false;
+  unsigned long long* ctr = ptr<unsigned long long>(c->d_counters);
+  KGX_CUDA(c, cudaMemsetAsync(ctr, 0, 3 * 8, c->stream));
+  DevTable t{ptr<NodeTab>(c->d_node_tab), ptr<Entry>(c->d_tab), ptr<uint32_t>(c->d_pk_slot0), ptr<uint32_t>(c->d_pk_stride),
+             ptr<uint32_t>(c->d_grank), p.n_nodes, p.G};
+  DevIndex ix{ptr<uint2>(c->d_bm), ptr<uint32_t>(c->d_pending), c->n_words};
+  DevCols dc{s->pid, s->gpu, s->node, s->sm_util, s->mem_util, reinterpret_cast<const unsigned long long*>(s->used),
+             reinterpret_cast<const unsigned long long*>(s->ts_us), reinterpret_cast<const unsigned long long*>(s->node_off), s->n};
+  const int grid = int(std::min<uint64_t>(uint64_t(c->sm_count) * 8, std::max<uint64_t>(1, cdiv(s->n, 256))));
+  if (s->n) {
+    Timed tm(c, KGX_K_INGEST);
+    if (x) k_ingest<true, 0><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
+    else k_ingest<false, 0><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
+    tm.launches(1);
+    KGX_TRY(launch_check(c, "k_ingest"));
+  }
+  KGX_CUDA(c, cudaMemcpyAsync(c->h_counters, ctr, 3 * 8, cudaMemcpyDeviceToHost, c->stream));
+  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->stats.n_matched = c->h_counters[C_MATCHED];
+  c->stats.n_dropped = c->h_counters[C_DROPPED];
+  if (c->h_counters[C_NEW]) {  // churn: series seen for the first time
+    KGX_TRY(rebuild_index(c));
+    {
+      Timed tm(c, KGX_K_INGEST);
+      if (x) k_ingest<true, 1><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
+      else k_ingest<false, 1><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
+      tm.launches(1);
+      KGX_TRY(launch_check(c, "k_ingest churn pass"));
+    }
+    KGX_CUDA(c, cudaMemsetAsync(c->d_pending.p, 0, size_t(c->n_words) * 4, c->stream));
+  }
+  if (!x && c->n_series && s->n) {
+    Timed tm(c, KGX_K_FINALIZE);
+    k_finalize_r<<<cdiv(c->n_series, 256), 256, 0, c->stream>>>(acc_view(c), dc, ptr<unsigned long long>(c->d_gpu_total), p.G,
+                                                                c->seq, c->n_series, p.n_nodes);
+    tm.launches(1);
+    KGX_TRY(launch_check(c, "k_finalize_r"));
+  }
+  return KGX_OK;
+}
+
+int render_device_locked(kgx_ctx* c, size_t* len) {
+  if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_render before kgx_set_table");
+  if (c->n_tiles == 0) { c->last_len = 0; c->rendered = true; if (len) *len = 0; c->stats.rendered_bytes = 0; return KGX_OK; }
+  unsigned long long* ctr = ptr<unsigned long long>(c->d_counters);
+  {
+    Timed tm(c, KGX_K_OTHER);
+    KGX_CUDA(c, cudaMemsetAsync(ctr + C_TOTAL_LEN, 0, 2 * 8, c->stream));
+    KGX_CUDA(c, cudaMemsetAsync(c->d_tile_state.p, 0, size_t(c->n_tiles) * 8, c->stream));
+    KGX_CUDA(c, cudaMemsetAsync(c->d_node_body_off.p, 0xff, (size_t(c->plan.n_nodes) + 1) * 8, c->stream));
+  }
+  DevRender R{};
+  R.fam = ptr<FamMeta>(c->d_fam);
+  R.tiles = ptr<Tile>(c->d_tiles); R.n_tiles = c->n_tiles;
+  R.lbl_off = ptr<unsigned long long>(c->d_lbl_off); R.lbl_blob = ptr<uint8_t>(c->d_lbl_blob);
+  R.ser_gidx = ptr<uint32_t>(c->d_ser_gidx); R.gpu_total = ptr<unsigned long long>(c->d_gpu_total);
+  R.tile_state = ptr<unsigned long long>(c->d_tile_state); R.node_body_off = ptr<unsigned long long>(c->d_node_body_off);
+  R.out = ptr<uint8_t>(c->d_out); R.smem_bytes = c->render_smem;
+  {
+    Timed tm(c, KGX_K_RENDER);
+    const int grid = int(std::min<uint32_t>(c->n_tiles, uint32_t(c->render_grid)));
+    k_render<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, acc_view(c), ctr);
+    tm.launches(1);
+    KGX_TRY(launch_check(c, "k_render"));
+  }
+  KGX_CUDA(c, cudaMemcpyAsync(c->h_counters + C_TOTAL_LEN, ctr + C_TOTAL_LEN, 8, cudaMemcpyDeviceToHost, c->stream));
+  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->last_len = size_t(c->h_counters[C_TOTAL_LEN]);
+  c->rendered = true;
+  c->stats.rendered_bytes = c->last_len;
+  if (len) *len = c->last_len;
+  return KGX_OK;
+}
+
+}  // namespace
+
+// =============================== C ABI ========================================
+extern "C" {
+
+int kgx_abi_version(void) { return KGX_ABI_VERSION; }
+
+const char* kgx_strerror(int code) {
+  int i = -code;
+  return (i >= 0 && i < int(sizeof kErrNames / sizeof kErrNames[0])) ? kErrNames[i] : "unknown error";
+}
+
+const char* kgx_last_error(kgx_ctx* c) { return c ? c->err.c_str() : "null ctx"; }
+
+int kgx_create(int device, const kgx_opts* opts, kgx_ctx** out) {
+  if (!out || !opts) return KGX_E_INVAL;
+  *out = nullptr;
+  if (opts->abi_version != KGX_ABI_VERSION || opts->mode < 0 || opts->mode > 2) return KGX_E_INVAL;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return KGX_E_CUDA;  // no CPU fallback
+  if (cudaSetDevice(device) != cudaSuccess) return KGX_E_CUDA;
+  kgx_ctx* c = new (std::nothrow) kgx_ctx();
+  if (!c) return KGX_E_NOMEM;
+  c->device = device; c->mode = opts->mode; c->profile = opts->profile != 0;
+  if (opts->stream) c->stream = static_cast<cudaStream_t>(opts->stream);
+  else { if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return KGX_E_CUDA; } c->own_stream = true; }
+  cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
+  build_family_meta(c);
+  if (cudaMallocHost(reinterpret_cast<void**>(&c->h_counters), C_COUNT * 8) != cudaSuccess ||
+      dev_reserve(c, c->d_counters, C_COUNT * 8) != KGX_OK) { kgx_destroy(c); return KGX_E_CUDA; }
+  cudaMemsetAsync(c->d_counters.p, 0, C_COUNT * 8, c->stream);
+  *out = c;
+  return KGX_OK;
+}
+
+void kgx_destroy(kgx_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  free_table_state(c);
+  dev_free(c, c->d_fam); dev_free(c, c->d_counters); dev_free(c, c->d_block_sums);
+  for (auto& b : c->d_cols) dev_free(c, b);
+  for (auto& b : c->d_tmp) dev_free(c, b);
+  for (auto& r : c->regions) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+  if (c->h_counters) cudaFreeHost(c->h_counters);
+  if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+int kgx_set_table(kgx_ctx* c, const kgx_table* table) {
+  if (!c) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  if (!table) return fail(c, KGX_E_INVAL, "null table");
+  if (c->have_table && c->mode != KGX_MODE_X &&
+      (table->n_nodes != c->plan.n_nodes || table->gpus_per_node != c->plan.G))
+    return fail(c, KGX_E_INVAL, "R modes: n_nodes/gpus_per_node cannot change while series persist");
+  std::vector<Carried> carried;
+  KGX_TRY(collect_carried(c, &carried));
+  Plan np;
+  std::string err;
+  int rc = build_plan(c->mode, table, carried, &np, &err);
+  if (rc != KGX_OK) { c->err = err; return rc; }
+  free_table_state(c);
+  c->plan = std::move(np);
+  c->have_table = true;
+  KGX_TRY(upload_plan(c));
+  c->stats.n_slots = c->plan.n_slots;
+  if (!carried.empty()) {
+    const uint32_t n = uint32_t(carried.size());
+    std::vector<unsigned long long> used(n), total(n);
+    for (uint32_t i = 0; i < n; ++i) { used[i] = carried[i].used; total[i] = carried[i].total; }
+    KGX_TRY(upload(c, c->d_tmp[1], c->plan.carried_slot.data(), n));
+    KGX_TRY(upload(c, c->d_tmp[2], used.data(), n));
+    KGX_TRY(upload(c, c->d_tmp[3], total.data(), n));
+    k_set_bits<<<cdiv(n, 256), 256, 0, c->stream>>>(ptr<uint32_t>(c->d_tmp[1]), n, ptr<uint32_t>(c->d_pending));
+    KGX_TRY(rebuild_index(c));
+    k_seed_carried<<<cdiv(n, 256), 256, 0, c->stream>>>(ptr<uint32_t>(c->d_tmp[1]), ptr<unsigned long long>(c->d_tmp[2]),
+                                                        ptr<unsigned long long>(c->d_tmp[3]), n, ptr<uint2>(c->d_bm), acc_view(c));
+    c->stats.kernel_launches += 2;
+    KGX_CUDA(c, cudaMemsetAsync(c->d_pending.p, 0, size_t(c->n_words) * 4, c->stream));
+    KGX_TRY(launch_check(c, "carry-over"));
+    KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
+  return KGX_OK;
+}
+
+int kgx_ingest_device(kgx_ctx* c, const kgx_cols* cols) {
+  if (!c) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  if (!cols) return fail(c, KGX_E_INVAL, "null cols");
+  return ingest_device_locked(c, cols);
+}
+
+int kgx_ingest(kgx_ctx* c, const kgx_cols* cols) {
+  if (!c) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  if (!cols) return fail(c, KGX_E_INVAL, "null cols");
+  if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_ingest before kgx_set_table");
+  if (!cols->gpu_total) return fail(c, KGX_E_INVAL, "cols: gpu_total missing");
+  kgx_cols d = *cols;
+  const size_t n = size_t(cols->n);
+  const void* src[8] = {cols->pid, cols->gpu, cols->used, cols->node, cols->sm_util, cols->mem_util, cols->ts_us, cols->node_off};
+  const size_t bytes[8] = {n * 4, n * 4, n * 8, n * 4, n * 4, n * 4, n * 8, (size_t(c->plan.n_nodes) + 1) * 8};
+  const void* dst[8];
+  for (int k = 0; k < 8; ++k) {
+    dst[k] = nullptr;
+    if (!src[k]) continue;
+    KGX_TRY(dev_reserve(c, c->d_cols[k], bytes[k]));
+    if (bytes[k]) KGX_CUDA(c, cudaMemcpyAsync(c->d_cols[k].p, src[k], bytes[k], cudaMemcpyHostToDevice, c->stream));
+    dst[k] = c->d_cols[k].p;
+  }
+  d.pid = static_cast<const uint32_t*>(dst[0]); d.gpu = static_cast<const uint32_t*>(dst[1]);
+  d.used = static_cast<const uint64_t*>(dst[2]); d.node = static_cast<const uint32_t*>(dst[3]);
+  d.sm_util = static_cast<const uint32_t*>(dst[4]); d.mem_util = static_cast<const uint32_t*>(dst[5]);
+  d.ts_us = static_cast<const uint64_t*>(dst[6]); d.node_off = static_cast<const uint64_t*>(dst[7]);
+  return ingest_device_locked(c, &d);
+}
+
+int kgx_reset_window(kgx_ctx* c) {
+  if (!c) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  if (c->mode != KGX_MODE_X) return fail(c, KGX_E_STATE, "R modes never reset: GaugeVec children persist");
+  if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_reset_window before kgx_set_table");
+  Timed tm(c, KGX_K_OTHER);
+  for (int k = 0; k < 6; ++k)
+    if (c->n_series) KGX_CUDA(c, cudaMemsetAsync(c->d_acc[k].p, 0, size_t(c->n_series) * 8, c->stream));
+  KGX_CUDA(c, cudaMemsetAsync(c->d_node_live.p, 0, size_t(c->plan.n_nodes) * 4, c->stream));
+  c->rendered = false;
+  return KGX_OK;
+}
+
+int kgx_render_device(kgx_ctx* c, size_t* len) {
+  if (!c) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  return render_device_locked(c, len);
+}
+
+int kgx_render(kgx_ctx* c, uint8_t* out, size_t cap, size_t* len) {
+  if (!c || !len) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  KGX_TRY(render_device_locked(c, len));
+  if (*len > cap) return fail(c, KGX_E_NOSPACE, "output buffer too small");
+  if (*len) {
+    if (!out) return fail(c, KGX_E_INVAL, "null output buffer");
+    KGX_CUDA(c, cudaMemcpyAsync(out, c->d_out.p, *len, cudaMemcpyDeviceToHost, c->stream));
+    KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
+  return KGX_OK;
+}
+
+int kgx_body_device(kgx_ctx* c, const uint8_t** dptr, size_t* len) {
+  if (!c || !dptr || !len) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  if (!c->rendered) return fail(c, KGX_E_STATE, "no rendered body");
+  *dptr = ptr<uint8_t>(c->d_out); *len = c->last_len;
+  return KGX_OK;
+}
+
+int kgx_body_offsets(kgx_ctx* c, uint64_t* off, size_t n) {
+  if (!c || !off) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  if (!c->rendered) return fail(c, KGX_E_STATE, "no rendered body");
+  const size_t NN = c->plan.n_nodes;
+  if (n != NN + 1) return fail(c, KGX_E_INVAL, "offset array must have n_nodes+1 entries");
+  if (c->n_tiles == 0) { std::fill(off, off + n, 0); return KGX_OK; }
+  KGX_CUDA(c, cudaMemcpyAsync(off, c->d_node_body_off.p, n * 8, cudaMemcpyDeviceToHost, c->stream));
+  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  off[NN] = c->last_len;
+  for (size_t k = NN; k-- > 0;)  // nodes without series have an empty body
+    if (off[k] == ~0ull) off[k] = off[k + 1];
+  return KGX_OK;
+}
+
+int kgx_family_count(kgx_ctx* c) { return c ? int(c->fam.size()) : KGX_E_INVAL; }
+
+int kgx_family_info(kgx_ctx* c, int family, const char** name, const char** help, const char* const** names, int* n_labels) {
+  if (!c || family < 0 || family >= int(c->fam.size())) return KGX_E_INVAL;
+  const FamilyDef& f = families(c->mode)[size_t(family)];
+  if (name) *name = f.name;
+  if (help) *help = f.help;
+  int nl = 0;
+  const char* const* ln = label_names(c->mode, &nl);
+  if (names) *names = ln;
+  if (n_labels) *n_labels = nl;
+  return KGX_OK;
+}
+
+int kgx_read_values(kgx_ctx* c, int family, double* values, uint32_t* slots, size_t cap, size_t* n_out) {
+  if (!c || !n_out) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_read_values before kgx_set_table");
+  if (family < 0 || family >= int(c->fam.size())) return fail(c, KGX_E_INVAL, "family index out of range");
+  const uint32_t S = c->n_series;
+  *n_out = 0;
+  if (!S) return KGX_OK;
+  KGX_TRY(dev_reserve(c, c->d_tmp[1], size_t(S) * 8));
+  KGX_TRY(dev_reserve(c, c->d_tmp[2], size_t(S)));
+  DevRender R{};
+  R.ser_gidx = ptr<uint32_t>(c->d_ser_gidx); R.gpu_total = ptr<unsigned long long>(c->d_gpu_total);
+  k_values<<<cdiv(S, 256), 256, 0, c->stream>>>(R, acc_view(c), c->fam[size_t(family)].kind, S, ptr<double>(c->d_tmp[1]),
+                                                ptr<uint8_t>(c->d_tmp[2]));
+  c->stats.kernel_launches += 1;
+  KGX_TRY(launch_check(c, "k_values"));
+  std::vector<double> v(S);
+  std::vector<uint8_t> live(S);
+  std::vector<uint32_t> slot(S);
+  KGX_CUDA(c, cudaMemcpyAsync(v.data(), c->d_tmp[1].p, size_t(S) * 8, cudaMemcpyDeviceToHost, c->stream));
+  KGX_CUDA(c, cudaMemcpyAsync(live.data(), c->d_tmp[2].p, S, cudaMemcpyDeviceToHost, c->stream));
+  KGX_CUDA(c, cudaMemcpyAsync(slot.data(), c->d_ser_slot.p, size_t(S) * 4, cudaMemcpyDeviceToHost, c->stream));
+  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  size_t n = 0;
+  for (uint32_t r = 0; r < S; ++r) {
+    if (!live[r]) continue;
+    if (n < cap) { if (values) values[n] = v[r]; if (slots) slots[n] = slot[r]; }
+    ++n;
+  }
+  *n_out = n;
+  return n <= cap ? KGX_OK : fail(c, KGX_E_NOSPACE, "value buffer too small");
+}
+
+int kgx_slot_labels(kgx_ctx* c, uint32_t slot, char* out, size_t cap, size_t* len) {
+  if (!c || !len) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  if (!c->have_table || slot >= c->plan.n_slots) return fail(c, KGX_E_INVAL, "slot out of range");
+  const Plan& p = c->plan;
+  size_t lo = 0, hi = p.runs.size();
+  while (hi - lo > 1) { size_t mid = (lo + hi) / 2; if (p.runs[mid].slot_start <= slot) lo = mid; else hi = mid; }
+  const Run& r = p.runs[lo];
+  const uint32_t a = r.a_first + (slot - r.slot_start);
+  std::string s(p.A_blob, size_t(p.A_off[a]), size_t(p.A_off[a + 1] - p.A_off[a]));
+  if (r.gidx != 0xFFFFFFFFu) s.append(p.G_blob, size_t(p.G_off[r.gidx]), size_t(p.G_off[r.gidx + 1] - p.G_off[r.gidx]));
+  s.append(p.B_blob, size_t(p.B_off[a]), size_t(p.B_off[a + 1] - p.B_off[a]));
+  *len = s.size();
+  if (out && cap) memcpy(out, s.data(), std::min(cap, s.size()));
+  return KGX_OK;
+}
+
+int kgx_format_values(kgx_ctx* c, const double* values, size_t n, uint8_t* out32) {
+  if (!c || (n && (!values || !out32))) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  if (!n) return KGX_OK;
+  KGX_TRY(dev_reserve(c, c->d_tmp[1], n * 8));
+  KGX_TRY(dev_reserve(c, c->d_tmp[2], n * 32));
+  KGX_CUDA(c, cudaMemcpyAsync(c->d_tmp[1].p, values, n * 8, cudaMemcpyHostToDevice, c->stream));
+  k_format_values<<<cdiv(n, 256), 256, 0, c->stream>>>(ptr<double>(c->d_tmp[1]), n, ptr<uint8_t>(c->d_tmp[2]));
+  c->stats.kernel_launches += 1;
+  KGX_TRY(launch_check(c, "k_format_values"));
+  KGX_CUDA(c, cudaMemcpyAsync(out32, c->d_tmp[2].p, n * 32, cudaMemcpyDeviceToHost, c->stream));
+  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  return KGX_OK;
+}
+
+void* kgx_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) return nullptr;
+  return p;
+}
+void kgx_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+int kgx_get_stats(kgx_ctx* c, kgx_stats* out) {
+  if (!c || !out) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  c->stats.n_series = c->n_series;
+  c->stats.device_bytes = c->device_bytes;
+  *out = c->stats;
+  return KGX_OK;
+}
+
+int kgx_sync(kgx_ctx* c) {
+  if (!c) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  return KGX_OK;
+}
+
+int kgx_get_profile(kgx_ctx* c, kgx_profile* out) {
+  if (!c || !out) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  for (auto& r : c->regions) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) c->prof.ms[r.kind] += ms;
+    cudaEventDestroy(r.a); cudaEventDestroy(r.b);
+  }
+  c->regions.clear();
+  *out = c->prof;
+  return KGX_OK;
+}
+
+int kgx_profile_reset(kgx_ctx* c) {
+  if (!c) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  for (auto& r : c->regions) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+  c->regions.clear();
+  c->prof = kgx_profile{};
+  return KGX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,470 @@
+// kgx_kernels.cuh — sm_100a kernels of the join -> reduce -> render path.
+//
+//   k_ingest      hash join (open addressing, main.go:141-145) fused with the
+//                 per-series integer reduction (main.go:147-150's upsert; X
+//                 mode: sum / max / last-timestamp / count)
+//   k_finalize_r  R modes: fetch the values of each series' last writer
+//   k_render      exposition writer (main.go:69-71: Gather + expfmt): exact
+//                 line lengths -> block scan -> inter-tile decoupled look-back
+//                 -> byte scatter, all in one pass over the series
+//   index kernels series-index rebuild on churn (cold path)
+#pragma once
+#include <cstdint>
+#include "kgx_fmt.cuh"
+#include "kgx_table.hpp"
+
+namespace kgx {
+
+// ---- device views ------------------------------------------------------------
+struct DevTable {
+  const NodeTab* node_tab;
+  const Entry* tab;
+  const uint32_t* pk_slot0;   // X
+  const uint32_t* pk_stride;  // X
+  const uint32_t* grank;      // X
+  uint32_t n_nodes, G;
+};
+
+struct DevIndex {       // which potential series (slots) exist, and their rank
+  uint2* bm;            // [n_words] {bits, exclusive prefix popcount}
+  uint32_t* pending;    // [n_words] slots seen for the first time in this ingest
+  uint32_t n_words;
+};
+
+struct DevAcc {  // per-series state, indexed by rank
+  unsigned long long *sum_used, *max_used, *last_ts, *sum_sm, *sum_mem, *count;  // X
+  unsigned long long *r_seq, *r_used, *r_total;                                  // R
+  uint32_t* node_live;  // [n_nodes] series with a value in the current window
+};
+
+struct DevCols {
+  const uint32_t *pid, *gpu, *node, *sm_util, *mem_util;
+  const unsigned long long *used, *ts_us, *node_off;
+  uint64_t n;
+};
+
+// counters[]: 0 matched samples, 1 dropped samples, 2 new slots seen
+enum { C_MATCHED = 0, C_DROPPED = 1, C_NEW = 2, C_TOTAL_LEN = 3, C_TICKET = 4, C_COUNT = 8 };
+
+__device__ __forceinline__ uint32_t dev_hash_pid(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+  return x;
+}
+
+// ---- ingest: join + reduce ---------------------------------------------------
+// PASS 0: normal pass.  Matches whose slot is not in the series index yet only
+//         mark it pending (the host then rebuilds the index and runs PASS 1).
+// PASS 1: churn pass, after the rebuild: folds exactly the matches PASS 0 had
+//         to skip (slot pending).
+template <bool XMODE, int PASS>
+__global__ void __launch_bounds__(256) k_ingest(DevTable t, DevIndex ix, DevAcc acc, DevCols c, uint32_t seq,
+                                                 unsigned long long* counters) {
+  unsigned long long matched = 0, dropped = 0;
+  bool any_new = false;
+  for (uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; i < c.n; i += uint64_t(gridDim.x) * blockDim.x) {
+    uint32_t node = 0;
+    if (c.node) node = c.node[i];
+    else if (c.node_off) {  // rows grouped by node: find the group
+      uint32_t lo = 0, hi = t.n_nodes;
+      while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (c.node_off[mid] <= i) lo = mid; else hi = mid; }
+      node = lo;
+    }
+    const uint32_t gpu = c.gpu[i];
+    if (node >= t.n_nodes || gpu >= t.G) { ++dropped; continue; }
+    const uint32_t pid = c.pid[i];
+    const NodeTab nt = t.node_tab[node];
+    uint32_t pos = uint32_t((uint64_t(dev_hash_pid(pid)) * nt.cap) >> 32);
+    bool hit = false;
+    for (;;) {
+      const Entry e = t.tab[nt.off + pos];
+      if (e.val == kEmpty) break;
+      if (e.key == pid) {
+        hit = true;
+        const uint32_t target = e.val & ~kMore;
+        uint32_t slot;
+        if (XMODE) slot = t.pk_slot0[target] + t.grank[node * t.G + gpu] * t.pk_stride[target];
+        else slot = target;
+        const uint32_t w = slot >> 5, bit = 1u << (slot & 31);
+        const uint2 b = ix.bm[w];
+        bool fold;
+        if (PASS == 0) {
+          fold = (b.x & bit) != 0;
+          if (!fold) { atomicOr(&ix.pending[w], bit); any_new = true; }
+        } else {
+          fold = (ix.pending[w] & bit) != 0;
+        }
+        if (fold) {
+          const uint32_t r = b.y + __popc(b.x & (bit - 1));
+          if (XMODE) {
+            const unsigned long long used = c.used[i];
+            if (atomicAdd(&acc.count[r], 1ull) == 0) atomicAdd(&acc.node_live[node], 1u);
+            atomicAdd(&acc.sum_used[r], used);
+            atomicMax(&acc.max_used[r], used);
+            atomicMax(&acc.last_ts[r], c.ts_us[i]);
+            atomicAdd(&acc.sum_sm[r], (unsigned long long)c.sm_util[i]);
+            atomicAdd(&acc.sum_mem[r], (unsigned long long)c.mem_util[i]);
+          } else {
+            // GaugeVec.Set: the last write in sample order wins (main.go:147,150)
+            atomicMax(&acc.r_seq[r], (uint64_t(seq) << 32) | uint64_t(i));
+          }
+        }
+        if (!(e.val & kMore)) break;
+      }
+      pos = pos + 1 == nt.cap ? 0 : pos + 1;
+    }
+    if (hit) ++matched; else ++dropped;
+  }
+  if (PASS == 0) {
+    // block-level reduction of the statistics
+    matched = __reduce_add_sync(0xffffffffu, uint32_t(matched));
+    dropped = __reduce_add_sync(0xffffffffu, uint32_t(dropped));
+    const bool warp_new = __any_sync(0xffffffffu, any_new);
+    if ((threadIdx.x & 31) == 0) {
+      if (matched) atomicAdd(&counters[C_MATCHED], matched);
+      if (dropped) atomicAdd(&counters[C_DROPPED], dropped);
+      if (warp_new) atomicAdd(&counters[C_NEW], 1ull);
+    }
+  }
+}
+
+// R modes: after the join, a series whose last writer is in this batch takes
+// that sample's values: float64(used) and the device's total (main.go:147,149).
+__global__ void k_finalize_r(DevAcc acc, DevCols c, const unsigned long long* gpu_total, uint32_t G, uint32_t seq,
+                             uint32_t n_series, uint32_t n_nodes) {
+  const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n_series) return;
+  const unsigned long long s = acc.r_seq[r];
+  if (uint32_t(s >> 32) != seq) return;
+  const uint64_t i = s & 0xffffffffull;
+  uint32_t node = 0;
+  if (c.node) node = c.node[i];
+  else if (c.node_off) {
+    uint32_t lo = 0, hi = n_nodes;
+    while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (c.node_off[mid] <= i) lo = mid; else hi = mid; }
+    node = lo;
+  }
+  acc.r_used[r] = c.used[i];
+  acc.r_total[r] = gpu_total[node * G + c.gpu[i]];
+}
+
+// ---- series index rebuild (cold path, on churn) ----------------------------------
+__global__ void k_merge_pending(uint2* bm, const uint32_t* pending, uint32_t n_words, uint32_t* popc_out) {
+  const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= n_words) return;
+  uint2 b = bm[w];
+  b.x |= pending[w];
+  bm[w] = b;
+  popc_out[w] = __popc(b.x);
+}
+
+// generic 3-step exclusive scan (u32 in, u64 out), 1024 items per block
+constexpr int kScanBlock = 256, kScanItems = 4;
+__global__ void k_scan_reduce(const uint32_t* in, uint64_t n, unsigned long long* block_sums) {
+  __shared__ unsigned long long sh[kScanBlock / 32];
+  const uint64_t base = uint64_t(blockIdx.x) * kScanBlock * kScanItems;
+  unsigned long long s = 0;
+  for (int k = 0; k < kScanItems; ++k) {
+    const uint64_t i = base + uint64_t(k) * kScanBlock + threadIdx.x;
+    if (i < n) s += in[i];
+  }
+  for (int o = 16; o; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) { unsigned long long tot = 0; for (int k = 0; k < kScanBlock / 32; ++k) tot += sh[k]; block_sums[blockIdx.x] = tot; }
+}
+__global__ void k_scan_blocksums(unsigned long long* block_sums, uint32_t nb, unsigned long long* total) {
+  // single block, serial over chunks of 1024
+  __shared__ unsigned long long sh[1024];
+  __shared__ unsigned long long carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (uint32_t base = 0; base < nb; base += 1024) {
+    const uint32_t i = base + threadIdx.x;
+    unsigned long long v = i < nb ? block_sums[i] : 0;
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+      unsigned long long t = threadIdx.x >= o ? sh[threadIdx.x - o] : 0;
+      __syncthreads();
+      sh[threadIdx.x] += t;
+      __syncthreads();
+    }
+    if (i < nb) block_sums[i] = carry + sh[threadIdx.x] - v;
+    __syncthreads();
+    if (threadIdx.x == 0) carry += sh[1023];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *total = carry;
+}
+// item layout inside a block: thread-major chunks of kScanItems consecutive items
+__global__ void k_scan_apply(const uint32_t* in, uint64_t n, const unsigned long long* block_sums, unsigned long long* out64,
+                             uint32_t* out32) {
+  __shared__ unsigned long long sh[kScanBlock / 32];
+  const uint64_t base = uint64_t(blockIdx.x) * kScanBlock * kScanItems + uint64_t(threadIdx.x) * kScanItems;
+  uint32_t v[kScanItems];
+  unsigned long long s = 0;
+  for (int k = 0; k < kScanItems; ++k) { v[k] = base + k < n ? in[base + k] : 0; s += v[k]; }
+  unsigned long long inc = s;
+  for (int o = 1; o < 32; o <<= 1) { unsigned long long t = __shfl_up_sync(0xffffffffu, inc, o); if ((threadIdx.x & 31) >= o) inc += t; }
+  if ((threadIdx.x & 31) == 31) sh[threadIdx.x >> 5] = inc;
+  __syncthreads();
+  unsigned long long warp_off = 0;
+  for (int k = 0; k < int(threadIdx.x >> 5); ++k) warp_off += sh[k];
+  unsigned long long run = block_sums[blockIdx.x] + warp_off + inc - s;
+  for (int k = 0; k < kScanItems; ++k) {
+    if (base + k < n) { if (out64) out64[base + k] = run; if (out32) out32[base + k] = uint32_t(run); }
+    run += v[k];
+  }
+}
+
+__global__ void k_set_prefix(uint2* bm, const uint32_t* prefix, uint32_t n_words) {
+  const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w < n_words) bm[w].y = prefix[w];
+}
+
+struct DevLabels {  // label pieces: text of slot = A[a] + G[gidx] + B[a]
+  const uint8_t *A_blob, *B_blob, *G_blob;
+  const unsigned long long *A_off, *B_off, *G_off;
+  const Run* runs;
+  uint32_t n_runs;
+};
+
+// one thread per bitmap word: emit the series of its set bits
+__global__ void k_build_series(const uint2* bm, uint32_t n_words, DevLabels L, uint32_t* ser_slot, uint32_t* ser_a,
+                               uint32_t* ser_gidx, uint32_t* ser_len) {
+  const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= n_words) return;
+  uint2 b = bm[w];
+  uint32_t bits = b.x, r = b.y;
+  while (bits) {
+    const uint32_t slot = (w << 5) + (__ffs(bits) - 1);
+    bits &= bits - 1;
+    uint32_t lo = 0, hi = L.n_runs;  // last run with slot_start <= slot
+    while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (L.runs[mid].slot_start <= slot) lo = mid; else hi = mid; }
+    const Run run = L.runs[lo];
+    const uint32_t a = run.a_first + (slot - run.slot_start);
+    uint32_t len = uint32_t(L.A_off[a + 1] - L.A_off[a]) + uint32_t(L.B_off[a + 1] - L.B_off[a]);
+    if (run.gidx != 0xFFFFFFFFu) len += uint32_t(L.G_off[run.gidx + 1] - L.G_off[run.gidx]);
+    ser_slot[r] = slot; ser_a[r] = a; ser_gidx[r] = run.gidx; ser_len[r] = len;
+    ++r;
+  }
+}
+
+// one warp per series: concatenate its label pieces into the series label blob
+__global__ void k_fill_labels(DevLabels L, const uint32_t* ser_a, const uint32_t* ser_gidx, const unsigned long long* lbl_off,
+                              uint32_t n_series, uint8_t* blob) {
+  const uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (r >= n_series) return;
+  const uint32_t a = ser_a[r], g = ser_gidx[r];
+  uint8_t* dst = blob + lbl_off[r];
+  const uint32_t la = uint32_t(L.A_off[a + 1] - L.A_off[a]);
+  for (uint32_t i = lane; i < la; i += 32) dst[i] = L.A_blob[L.A_off[a] + i];
+  dst += la;
+  if (g != 0xFFFFFFFFu) {
+    const uint32_t lg = uint32_t(L.G_off[g + 1] - L.G_off[g]);
+    for (uint32_t i = lane; i < lg; i += 32) dst[i] = L.G_blob[L.G_off[g] + i];
+    dst += lg;
+  }
+  const uint32_t lb = uint32_t(L.B_off[a + 1] - L.B_off[a]);
+  for (uint32_t i = lane; i < lb; i += 32) dst[i] = L.B_blob[L.B_off[a] + i];
+}
+
+__device__ __forceinline__ uint32_t rank_of(const uint2* bm, uint32_t slot) {
+  const uint2 b = bm[slot >> 5];
+  return b.y + __popc(b.x & ((1u << (slot & 31)) - 1));
+}
+
+// move per-series state from the old ranks to the new ones
+__global__ void k_remap(const uint32_t* old_slot, uint32_t n_old, const uint2* bm, int n_arrays,
+                        const unsigned long long* const* old_arr, unsigned long long* const* new_arr) {
+  const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n_old) return;
+  const uint32_t nr = rank_of(bm, old_slot[r]);
+  for (int k = 0; k < n_arrays; ++k) new_arr[k][nr] = old_arr[k][r];
+}
+
+__global__ void k_node_ranks(const uint2* bm, const uint32_t* node_slot_base, uint32_t n_nodes, uint32_t n_slots,
+                             uint32_t n_series, uint32_t* node_ser_off) {
+  const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n > n_nodes) return;
+  const uint32_t s = node_slot_base[n];
+  node_ser_off[n] = s >= n_slots ? n_series : rank_of(bm, s);
+}
+
+// R modes, table change: seed carried series (slot, used, total)
+__global__ void k_seed_carried(const uint32_t* slots, const unsigned long long* used, const unsigned long long* total,
+                               uint32_t n, const uint2* bm, DevAcc acc) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t r = rank_of(bm, slots[i]);
+  acc.r_seq[r] = 1;  // older than any ingest (their seq starts at 1)
+  acc.r_used[r] = used[i];
+  acc.r_total[r] = total[i];
+}
+__global__ void k_set_bits(const uint32_t* slots, uint32_t n, uint32_t* pending) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) atomicOr(&pending[slots[i] >> 5], 1u << (slots[i] & 31));
+}
+
+// ---- render --------------------------------------------------------------------------
+struct FamMeta {
+  uint8_t name[64];
+  uint8_t header[320];  // "# HELP <name> <help>\n# TYPE <name> gauge\n"
+  uint32_t name_len, header_len;
+  int32_t kind;
+  int32_t pad;
+};
+constexpr int kMaxFamilies = 8;
+
+struct Tile {
+  uint32_t first;   // rank of the first series
+  uint32_t node;
+  uint16_t count;   // series in the tile
+  uint8_t family;
+  uint8_t flags;    // bit0: first tile of (node, family): carries the header
+                    // bit1: first tile of the node: records the body offset
+};
+
+struct DevRender {
+  const FamMeta* fam;  // [n_families], device global memory (one schema per ctx)
+  const Tile* tiles;
+  uint32_t n_tiles;
+  const unsigned long long* lbl_off;  // [n_series+1]
+  const uint8_t* lbl_blob;
+  const uint32_t* ser_gidx;
+  const unsigned long long* gpu_total;  // X: [n_nodes*G]
+  unsigned long long* tile_state;       // [n_tiles] look-back words
+  unsigned long long* node_body_off;    // [n_nodes+1]
+  uint8_t* out;
+  uint32_t smem_bytes;                  // capacity of the tile buffer
+};
+
+constexpr unsigned long long kStAgg = 1ull << 62, kStPrefix = 2ull << 62, kStMask = 3ull << 62;
+
+__device__ __forceinline__ double series_value(int kind, const DevAcc& acc, const DevRender& R, uint32_t r, bool& live) {
+  switch (kind) {
+    case V_R_USED: live = acc.r_seq[r] != 0; return __ull2double_rn(acc.r_used[r]);            // main.go:147
+    case V_R_PERC: live = acc.r_seq[r] != 0;                                                    // main.go:149
+      return __dmul_rn(__ddiv_rn(__ull2double_rn(acc.r_used[r]), __ull2double_rn(acc.r_total[r])), 100.0);
+    case V_X_SUM: live = acc.count[r] != 0; return __ull2double_rn(acc.sum_used[r]);
+    case V_X_PERC: live = acc.count[r] != 0;
+      return __dmul_rn(__ddiv_rn(__ull2double_rn(acc.sum_used[r]), __ull2double_rn(R.gpu_total[R.ser_gidx[r]])), 100.0);
+    case V_X_MAX: live = acc.count[r] != 0; return __ull2double_rn(acc.max_used[r]);
+    case V_X_SM: live = acc.count[r] != 0; return __ddiv_rn(__ull2double_rn(acc.sum_sm[r]), __ull2double_rn(acc.count[r]));
+    case V_X_MEM: live = acc.count[r] != 0; return __ddiv_rn(__ull2double_rn(acc.sum_mem[r]), __ull2double_rn(acc.count[r]));
+    default: live = acc.count[r] != 0; return __ddiv_rn(__ull2double_rn(acc.last_ts[r]), 1e6);
+  }
+}
+
+constexpr int kRenderThreads = 256;
+
+// One CTA per tile (taken in ticket order so look-back never waits on a tile
+// that has not started).  v1 writer: every thread composes its own line in the
+// shared-memory tile buffer, then the CTA streams the buffer out coalesced.
+__global__ void __launch_bounds__(kRenderThreads) k_render(DevRender R, DevAcc acc, unsigned long long* counters) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  __shared__ uint32_t s_warp[kRenderThreads / 32];
+  __shared__ uint32_t s_tile;
+  __shared__ unsigned long long s_base;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) s_tile = uint32_t(atomicAdd(&counters[C_TICKET], 1ull));
+    __syncthreads();
+    const uint32_t t = s_tile;
+    if (t >= R.n_tiles) return;
+    const Tile tile = R.tiles[t];
+    const FamMeta& fm = R.fam[tile.family];
+    // ---- pass 1: exact length of every line
+    uint8_t txt[kMaxValueText];
+    int vlen = 0;
+    uint32_t len = 0, lbl_len = 0;
+    unsigned long long lbl_at = 0;
+    if (tid < tile.count) {
+      const uint32_t r = tile.first + tid;
+      bool live;
+      const double v = series_value(fm.kind, acc, R, r, live);
+      if (live) {
+        vlen = format_value(v, txt);
+        lbl_at = R.lbl_off[r];
+        lbl_len = uint32_t(R.lbl_off[r + 1] - lbl_at);
+        len = fm.name_len + lbl_len + 1 + uint32_t(vlen) + 1;
+      }
+    }
+    const uint32_t hdr = ((tile.flags & 1) && acc.node_live[tile.node] != 0) ? fm.header_len : 0;
+    // ---- exclusive scan of the line lengths over the CTA
+    uint32_t inc = len;
+    for (int o = 1; o < 32; o <<= 1) { uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
+    if (lane == 31) s_warp[wid] = inc;
+    __syncthreads();
+    uint32_t woff = 0, total = hdr;
+    for (int k = 0; k < kRenderThreads / 32; ++k) { if (k < int(wid)) woff += s_warp[k]; total += s_warp[k]; }
+    const uint32_t off = hdr + woff + inc - len;
+    // ---- inter-tile offset: decoupled look-back over the tile chain
+    if (tid == 0) {
+      unsigned long long base = 0;
+      if (t > 0) {
+        atomicExch(&R.tile_state[t], kStAgg | total);
+        for (uint32_t p = t; p-- > 0;) {
+          unsigned long long s;
+          do { s = *(volatile unsigned long long*)&R.tile_state[p]; } while ((s & kStMask) == 0);
+          base += s & ~kStMask;
+          if ((s & kStMask) == kStPrefix) break;
+        }
+      }
+      atomicExch(&R.tile_state[t], kStPrefix | (base + total));
+      s_base = base;
+      if (tile.flags & 2) R.node_body_off[tile.node] = base;
+      if (t == R.n_tiles - 1) counters[C_TOTAL_LEN] = base + total;
+    }
+    __syncthreads();
+    const unsigned long long base = s_base;
+    const uint32_t shift = uint32_t(base & 15);  // keep smem and global congruent mod 16
+    // ---- pass 2: compose the tile text in shared memory
+    uint8_t* buf = smem + shift;
+    if (hdr) for (uint32_t i = tid; i < hdr; i += kRenderThreads) buf[i] = fm.header[i];
+    if (len) {
+      uint8_t* p = buf + off;
+      for (uint32_t i = 0; i < fm.name_len; ++i) p[i] = fm.name[i];
+      p += fm.name_len;
+      const uint8_t* src = R.lbl_blob + lbl_at;
+      for (uint32_t i = 0; i < lbl_len; ++i) p[i] = src[i];
+      p += lbl_len;
+      *p++ = ' ';
+      for (int i = 0; i < vlen; ++i) p[i] = txt[i];
+      p[vlen] = '\n';
+    }
+    __syncthreads();
+    // ---- stream the tile out: byte head/tail, 16-byte body
+    uint8_t* g = R.out + base;
+    const uint32_t head = min(total, (16u - shift) & 15u);
+    const uint32_t body = (total - head) & ~15u;
+    if (tid < head) g[tid] = buf[tid];
+    const uint4* sb = reinterpret_cast<const uint4*>(buf + head);
+    uint4* gb = reinterpret_cast<uint4*>(g + head);
+    for (uint32_t i = tid; i < body / 16; i += kRenderThreads) gb[i] = sb[i];
+    for (uint32_t i = head + body + tid; i < total; i += kRenderThreads) g[i] = buf[i];
+  }
+}
+
+// ---- values only (Collector read-back) -----------------------------------------------
+__global__ void k_values(DevRender R, DevAcc acc, int kind, uint32_t n_series, double* values, uint8_t* live_out) {
+  const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n_series) return;
+  bool live;
+  values[r] = series_value(kind, acc, R, r, live);
+  live_out[r] = live;
+}
+
+// ---- float printer entry (tests) ---------------------------------------------------------
+__global__ void k_format_values(const double* v, uint64_t n, uint8_t* out32) {
+  const uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
+  if (i >= n) return;
+  uint8_t txt[kMaxValueText];
+  const int len = format_value(v[i], txt);
+  uint8_t* rec = out32 + 32 * i;
+  for (int k = 0; k < 31; ++k) rec[k] = k < len ? txt[k] : 0;
+  rec[31] = uint8_t(len);
+}
+
+}  // namespace kgx

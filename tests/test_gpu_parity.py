@@ -1,0 +1,246 @@
+"""GPU parity tests: the CUDA path behind the C ABI against the CPU oracle on
+the same seeded inputs.  Bar: /metrics bytes bit-exact."""
+import os
+
+import numpy as np
+import pytest
+
+from goformat_model import go_format
+from kgx_b200.abi import Cols, Table, MODE_R_INTENDED, MODE_R_LITERAL, MODE_X
+from kgx_b200.fleet import Fleet, GIB
+from kgx_b200 import kgx, build
+from test_oracle_format import KAT
+from test_oracle_semantics import _cols, _tbl
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _built():
+    build.build()
+
+
+def _pair(kgo, mode, threads=1):
+    return kgx.Kgx(mode), kgo.Oracle(mode, kgo.JOIN_HASH, threads)
+
+
+def _same(g, o):
+    gb, ob = g.render(), o.render()
+    if gb != ob:
+        gl, ol = gb.split(b"\n"), ob.split(b"\n")
+        for i, (a, b) in enumerate(zip(gl, ol)):
+            assert a == b, "line %d differs:\n gpu: %r\n cpu: %r" % (i, a, b)
+        assert len(gl) == len(ol), "line counts differ: gpu %d cpu %d" % (len(gl), len(ol))
+    assert list(g.body_offsets()) == list(o.body_offsets())
+    return gb
+
+
+def test_float_printer_known_answers():
+    g = kgx.Kgx(MODE_R_INTENDED)
+    vals = np.array([v for v, _ in KAT], dtype=np.float64)
+    out = g.format_values(vals)
+    for (v, want), rec in zip(KAT, out):
+        assert bytes(rec[:rec[31]]).decode() == want, (v, bytes(rec[:rec[31]]), want)
+
+
+def test_float_printer_vs_oracle_and_repr(kgo):
+    g = kgx.Kgx(MODE_R_INTENDED)
+    rng = np.random.default_rng(0xB200)
+    bits = rng.integers(0, 2**64, size=2_000_000, dtype=np.uint64)
+    vals = bits.view(np.float64).copy()
+    used = rng.integers(1, 65537, size=200_000).astype(np.uint64) * np.uint64(2 << 20)
+    dom = np.concatenate([used.astype(np.float64), used.astype(np.float64) / np.float64(192 * GIB) * 100,
+                          rng.integers(0, 5000, 200_000) / rng.integers(1, 50, 200_000),
+                          rng.integers(1_790_000_000_000_000, 1_790_000_010_000_000_000, 200_000).astype(np.float64) / 1e6,
+                          np.ldexp(1.0, np.arange(-1074, 1024)), np.arange(0, 4096, dtype=np.float64)])
+    vals = np.concatenate([vals, dom, -dom[:1000]])
+    got = g.format_values(vals)
+    want = kgo.format_values(vals)
+    bad = np.nonzero((got != want).any(axis=1))[0]
+    assert len(bad) == 0, (vals[bad[0]].hex(), bytes(got[bad[0]]), bytes(want[bad[0]]))
+    for i in rng.integers(0, len(vals), 20000):  # and against CPython's repr directly
+        assert bytes(got[i][:got[i][31]]).decode() == go_format(float(vals[i]))
+
+
+def test_float_printer_golden_fixture():
+    fx = np.load(os.path.join(GOLD, "float_text.npz"))
+    g = kgx.Kgx(MODE_R_INTENDED)
+    got = g.format_values(fx["bits"].view(np.float64))
+    assert (got == fx["text"]).all()
+
+
+def test_whole_body_golden(kgo):
+    g = kgx.Kgx(MODE_R_INTENDED)
+    g.set_table(_tbl([(0, "trainer-0", [1, 4242, 77]), (0, "idle", [5, 6])]))
+    g.ingest(_cols([(4242, 0, 1 * GIB), (999, 1, 5 * GIB)]))
+    assert g.render() == open(os.path.join(GOLD, "r_single.txt"), "rb").read()
+    st = g.stats()
+    assert st["n_matched"] == 1 and st["n_dropped"] == 1 and st["n_series"] == 1
+
+
+def test_empty_inputs(kgo):
+    g, o = _pair(kgo, MODE_R_INTENDED)
+    t = _tbl([(0, "p", [10])])
+    g.set_table(t); o.set_table(t)
+    for rows in ([(11, 0, 1)], []):
+        c = _cols(rows)
+        g.ingest(c); o.ingest(c)
+        assert _same(g, o) == b""
+    e = _tbl([])
+    g2 = kgx.Kgx(MODE_R_INTENDED)
+    g2.set_table(e)
+    g2.ingest(_cols([(1, 0, 1)]))
+    assert g2.render() == b""
+
+
+def test_literal_golden(kgo):
+    g, o = _pair(kgo, MODE_R_LITERAL)
+    t = _tbl([(0, "p", [1000, 2000, 3000]), (0, "q", [7])])
+    g.set_table(t); o.set_table(t)
+    c = _cols([(0, 0, 10), (2, 0, 30), (5, 0, 60)])
+    g.ingest(c); o.ingest(c)
+    body = _same(g, o).decode()
+    lines = [l for l in body.splitlines() if l.startswith("pod_gpu_memory_usage{")]
+    assert lines == ['pod_gpu_memory_usage{pid="0",pod="p"} 10', 'pod_gpu_memory_usage{pid="0",pod="q"} 10',
+                     'pod_gpu_memory_usage{pid="2",pod="p"} 30']
+
+
+def test_last_write_wins_persistence_and_table_change(kgo):
+    g, o = _pair(kgo, MODE_R_INTENDED)
+    t1 = _tbl([(0, "p", [7, 8]), (0, "gone", [9])])
+    g.set_table(t1); o.set_table(t1)
+    c = _cols([(7, 0, 100), (7, 1, 200), (8, 0, 5), (9, 2, 77)])
+    g.ingest(c); o.ingest(c)
+    assert b'pod_gpu_memory_usage{pid="7",pod="p"} 200\n' in _same(g, o)
+    # table rebuilt (main.go:84 every cycle): pid 8 and pod "gone" vanish, their children keep their values
+    t2 = _tbl([(0, "p", [7]), (0, "new", [8])])
+    g.set_table(t2); o.set_table(t2)
+    _same(g, o)
+    c = _cols([(7, 0, 300), (8, 0, 6)], total=40 * GIB)
+    g.ingest(c); o.ingest(c)
+    body = _same(g, o)
+    for want in (b'{pid="7",pod="p"} 300\n', b'{pid="8",pod="p"} 5\n', b'{pid="8",pod="new"} 6\n', b'{pid="9",pod="gone"} 77\n'):
+        assert b"pod_gpu_memory_usage" + want in body
+
+
+def test_escaping_special_values_and_duplicates(kgo):
+    g, o = _pair(kgo, MODE_R_INTENDED)
+    t = _tbl([(0, 'we"ird\\pod\nx', [1, 1, 1]), (0, "zero-total", [2]), (0, "héllo-✓", [1, 3]), (0, "", [4])])
+    g.set_table(t); o.set_table(t)
+    c = _cols([(1, 0, 2**64 - 1), (2, 1, 0), (3, 0, 12345), (4, 0, 1), (2, 9, 5)])  # last row: gpu out of range
+    c.gpu_total[1] = 0
+    g.ingest(c); o.ingest(c)
+    body = _same(g, o).decode()
+    assert 'pod="we\\"ird\\\\pod\\nx"} 1.8446744073709552e+19' in body
+    assert 'docker_gpu_memory_perc_usage{pid="2",pod="zero-total"} NaN' in body
+
+
+def test_invalid_inputs_rejected():
+    g = kgx.Kgx(MODE_R_INTENDED)
+    with pytest.raises(kgx.KgxError):
+        g.ingest(_cols([(1, 0, 1)]))  # no table yet
+    with pytest.raises(kgx.KgxError):
+        g.set_table(_tbl([(0, b"bad\xff", [1])]))  # invalid UTF-8: WithLabelValues would panic
+    with pytest.raises(kgx.KgxError):
+        g.set_table(_tbl([(0, "dup", [1]), (0, "dup", [2])]))
+    with pytest.raises(kgx.KgxError):
+        g.reset_window()
+    g.set_table(_tbl([(0, "p", [1])]))
+    small = np.zeros(8, dtype=np.uint8)
+    g.ingest(_cols([(1, 0, 1)]))
+    assert g.render_into(small) < 0  # KGX_E_NOSPACE reports the needed size
+
+
+@pytest.mark.parametrize("mode", [MODE_R_INTENDED, MODE_R_LITERAL, MODE_X])
+@pytest.mark.parametrize("cfg", [1, 2])
+def test_fleet_configs_bit_exact(kgo, mode, cfg):
+    f = Fleet.config(cfg)
+    t = f.table(mode)
+    g, o = _pair(kgo, mode, threads=4)
+    g.set_table(t); o.set_table(t)
+    s = f.scrape(0)
+    if mode == MODE_R_LITERAL:
+        s.pid = (s.pid % 40).astype(np.uint32)
+    g.ingest(s); o.ingest(s)
+    body = _same(g, o)
+    assert len(body) > 1000
+    st = g.stats()
+    assert st["n_series"] == o.series_count()
+    for fam in range(g.family_count()):
+        assert np.array_equal(g.read_values(fam), o.read_values(fam))
+
+
+@pytest.mark.parametrize("mode", [MODE_R_INTENDED, MODE_X])
+@pytest.mark.parametrize("shuffle", [False, True])
+def test_multi_node_fleet(kgo, mode, shuffle):
+    f = Fleet(n_nodes=37, pods=50, procs=400, seed=0xB200 + 3)
+    t = f.table(mode)
+    g, o = _pair(kgo, mode, threads=4)
+    g.set_table(t); o.set_table(t)
+    s = f.scrape(0, shuffle_nodes=shuffle)
+    if not shuffle:
+        s.node = None  # exercise the node_off grouping path
+    g.ingest(s)
+    s2 = f.scrape(0, shuffle_nodes=shuffle)
+    o.ingest(s2)
+    _same(g, o)
+
+
+def test_x_window_of_scrapes_and_reset(kgo):
+    f = Fleet(n_nodes=4, pods=64, procs=512, seed=0xB200 + 5, scrapes=6)
+    t = f.table(MODE_X)
+    g, o = _pair(kgo, MODE_X, threads=2)
+    g.set_table(t); o.set_table(t)
+    for k in range(6):
+        s = f.scrape(k)
+        g.ingest(s); o.ingest(s)
+        if k in (0, 3, 5):
+            _same(g, o)
+    g.reset_window(); o.reset_window()
+    assert _same(g, o) == b""
+    s = f.scrape(7)
+    keep = (s.pid % 3) != 0  # some series stay empty in the new window: they must not be printed
+    s = Cols(pid=s.pid[keep], gpu=s.gpu[keep], used=s.used[keep], node=s.node[keep], sm_util=s.sm_util[keep],
+             mem_util=s.mem_util[keep], ts_us=s.ts_us[keep], gpu_total=s.gpu_total)
+    g.ingest(s); o.ingest(s)
+    assert len(_same(g, o)) > 0
+
+
+def test_r_staleness_over_cycles(kgo):
+    f = Fleet(n_nodes=3, pods=40, procs=300, seed=0xB200 + 5)
+    g, o = _pair(kgo, MODE_R_INTENDED)
+    t = f.table(MODE_R_INTENDED)
+    g.set_table(t); o.set_table(t)
+    for k in range(4):
+        s = f.scrape(k)
+        keep = ((s.pid + k) % 4) != 0  # processes come and go; vanished ones keep their last value
+        s = Cols(pid=s.pid[keep], gpu=s.gpu[keep], used=s.used[keep], node=s.node[keep], gpu_total=s.gpu_total)
+        g.ingest(s); o.ingest(s)
+        _same(g, o)
+
+
+def test_multimap_pid_in_several_pods(kgo):
+    for mode in (MODE_R_INTENDED, MODE_X):
+        if mode == MODE_X:
+            t = Table(1, 2, [0, 0, 0], ["a", "b", "c"], [0, 1, 2, 2], [1, 1, 1, 5], namespace=["n", "n", "n"],
+                      container=["x", "x", "y"], gpu_uuid=["GPU-1", "GPU-0"])
+            c = Cols(pid=[1, 5, 1], gpu=[0, 1, 1], used=[10, 20, 30], sm_util=[1, 2, 3], mem_util=[4, 5, 6],
+                     ts_us=[7, 8, 9], gpu_total=[100, 200])
+        else:
+            t = _tbl([(0, "a", [1]), (0, "b", [1, 2]), (0, "c", [1])])  # `ps` sees PID 1 in every container
+            c = _cols([(1, 0, 10), (2, 0, 20)])
+        g, o = _pair(kgo, mode)
+        g.set_table(t); o.set_table(t)
+        g.ingest(c); o.ingest(c)
+        assert len(_same(g, o)) > 0
+
+
+def test_long_labels_and_many_lines_per_tile(kgo):
+    pods = [(0, ("p%03d-" % i) + "x" * (i * 7 % 250), [1000 + i]) for i in range(300)]
+    t = _tbl(pods)
+    g, o = _pair(kgo, MODE_R_INTENDED)
+    g.set_table(t); o.set_table(t)
+    c = _cols([(1000 + i, i % 8, (i + 1) * 12345678901) for i in range(300)])
+    g.ingest(c); o.ingest(c)
+    _same(g, o)
