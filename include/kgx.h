@@ -233,6 +233,8 @@ void kgx_host_free(void* p);
 int kgx_get_stats(kgx_ctx* ctx, kgx_stats* out);
 int kgx_get_profile(kgx_ctx* ctx, kgx_profile* out);
 int kgx_profile_reset(kgx_ctx* ctx);
+/* Turn per-kernel event timing on (1) or off (0) after creation. */
+int kgx_set_profile(kgx_ctx* ctx, int on);
 /* Block until all work queued by this ctx has finished. */
 int kgx_sync(kgx_ctx* ctx);
 

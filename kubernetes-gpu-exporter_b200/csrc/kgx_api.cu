@@ -751,6 +751,13 @@ int kgx_get_profile(kgx_ctx* c, kgx_profile* out) {
   return KGX_OK;
 }
 
+int kgx_set_profile(kgx_ctx* c, int on) {
+  if (!c) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  c->profile = on != 0;
+  return KGX_OK;
+}
+
 int kgx_profile_reset(kgx_ctx* c) {
   if (!c) return KGX_E_INVAL;
   std::lock_guard<std::mutex> g(c->mu);

@@ -17,7 +17,7 @@ EXPORTS = [
     "kgx_abi_version", "kgx_strerror", "kgx_last_error", "kgx_create", "kgx_destroy", "kgx_set_table", "kgx_ingest",
     "kgx_ingest_device", "kgx_reset_window", "kgx_render_device", "kgx_render", "kgx_body_device", "kgx_body_offsets",
     "kgx_read_values", "kgx_family_count", "kgx_family_info", "kgx_slot_labels", "kgx_format_values", "kgx_host_alloc",
-    "kgx_host_free", "kgx_get_stats", "kgx_get_profile", "kgx_profile_reset", "kgx_sync",
+    "kgx_host_free", "kgx_get_stats", "kgx_get_profile", "kgx_profile_reset", "kgx_set_profile", "kgx_sync",
 ]
 
 
@@ -62,6 +62,7 @@ def lib():
         L.kgx_get_stats.argtypes = [vp, C.POINTER(abi.kgx_stats)]
         L.kgx_get_profile.argtypes = [vp, C.POINTER(abi.kgx_profile)]
         L.kgx_profile_reset.argtypes = [vp]
+        L.kgx_set_profile.argtypes = [vp, C.c_int]
         L.kgx_sync.argtypes = [vp]
         _LIB = L
     return _LIB
@@ -206,6 +207,9 @@ class Kgx:
         p = abi.kgx_profile()
         self._chk(lib().kgx_get_profile(self._h, C.byref(p)))
         return {abi.K_NAMES[i]: (p.ms[i], int(p.launches[i])) for i in range(abi.K_COUNT)}
+
+    def set_profile(self, on):
+        self._chk(lib().kgx_set_profile(self._h, int(on)))
 
     def profile_reset(self):
         self._chk(lib().kgx_profile_reset(self._h))
