@@ -1,0 +1,206 @@
+// Package kgx binds libkgx.so (include/kgx.h) for the exporter's Go host.
+//
+// NOT COMPILED ON THE BUILD BOX: there is no Go toolchain there (`go: command
+// not found`).  It is the reference-side binding a maintainer adds next to
+// main.go; see INTEGRATION.md.
+package kgx
+
+/*
+#cgo CFLAGS: -I${SRCDIR}/../../include
+#cgo LDFLAGS: -L${SRCDIR}/../../kubernetes-gpu-exporter_b200/csrc -lkgx
+#include <stdlib.h>
+#include "kgx.h"
+*/
+import "C"
+
+import (
+	"fmt"
+	"runtime"
+	"unsafe"
+)
+
+type Mode int
+
+const (
+	ModeRIntended Mode = C.KGX_MODE_R_INTENDED // main.go's families, PID value equality
+	ModeRLiteral  Mode = C.KGX_MODE_R_LITERAL  // main.go:144-145 exactly as written
+	ModeX         Mode = C.KGX_MODE_X          // (pod, namespace, container, gpu) reductions
+)
+
+type Ctx struct{ p *C.kgx_ctx }
+
+func (c *Ctx) err(rc C.int) error {
+	if rc == C.KGX_OK {
+		return nil
+	}
+	return fmt.Errorf("kgx: %s: %s", C.GoString(C.kgx_strerror(rc)), C.GoString(C.kgx_last_error(c.p)))
+}
+
+func New(device int, mode Mode) (*Ctx, error) {
+	opts := C.kgx_opts{abi_version: C.KGX_ABI_VERSION, mode: C.int32_t(mode)}
+	c := &Ctx{}
+	if rc := C.kgx_create(C.int(device), &opts, &c.p); rc != C.KGX_OK {
+		return nil, fmt.Errorf("kgx_create: %s (a CUDA device is required; there is no CPU fallback)", C.GoString(C.kgx_strerror(rc)))
+	}
+	runtime.SetFinalizer(c, func(c *Ctx) { c.Close() })
+	return c, nil
+}
+
+func (c *Ctx) Close() {
+	if c.p != nil {
+		C.kgx_destroy(c.p)
+		c.p = nil
+	}
+}
+
+// Table is the flat form of `podPIDMap map[string][]string` (main.go:84).
+// The library copies everything before returning, so Go memory may be passed
+// directly (no Go pointer is retained — the cgo rule).
+type Table struct {
+	Nodes, GPUsPerNode uint32
+	PodkeyNode         []uint32
+	Pod, Namespace, Container []string // Namespace/Container: X mode only
+	EntryPodkey, EntryPID     []uint32
+	GPUUUID                   []string // X mode only, index node*G+gpu
+}
+
+func pack(ss []string) (blob []byte, off []uint64) {
+	off = make([]uint64, len(ss)+1)
+	for i, s := range ss {
+		blob = append(blob, s...)
+		off[i+1] = uint64(len(blob))
+	}
+	blob = append(blob, 0)
+	return
+}
+
+func u32p(s []uint32) *C.uint32_t {
+	if len(s) == 0 {
+		return nil
+	}
+	return (*C.uint32_t)(unsafe.Pointer(&s[0]))
+}
+func u64p(s []uint64) *C.uint64_t {
+	if len(s) == 0 {
+		return nil
+	}
+	return (*C.uint64_t)(unsafe.Pointer(&s[0]))
+}
+
+func (c *Ctx) SetTable(t *Table) error {
+	var pin runtime.Pinner
+	defer pin.Unpin()
+	ct := C.kgx_table{n_nodes: C.uint32_t(t.Nodes), gpus_per_node: C.uint32_t(t.GPUsPerNode),
+		n_podkeys: C.uint64_t(len(t.PodkeyNode)), n_entries: C.uint64_t(len(t.EntryPID))}
+	set := func(ss []string, blob **C.char, off **C.uint64_t) {
+		if ss == nil {
+			return
+		}
+		b, o := pack(ss)
+		pin.Pin(&b[0])
+		pin.Pin(&o[0])
+		*blob, *off = (*C.char)(unsafe.Pointer(&b[0])), u64p(o)
+	}
+	set(t.Pod, &ct.pod_blob, &ct.pod_off)
+	set(t.Namespace, &ct.namespace_blob, &ct.namespace_off)
+	set(t.Container, &ct.container_blob, &ct.container_off)
+	set(t.GPUUUID, &ct.gpu_uuid_blob, &ct.gpu_uuid_off)
+	for _, s := range [][]uint32{t.PodkeyNode, t.EntryPodkey, t.EntryPID} {
+		if len(s) > 0 {
+			pin.Pin(&s[0])
+		}
+	}
+	ct.podkey_node, ct.entry_podkey, ct.entry_pid = u32p(t.PodkeyNode), u32p(t.EntryPodkey), u32p(t.EntryPID)
+	return c.err(C.kgx_set_table(c.p, &ct))
+}
+
+// Cols is one poll cycle's samples in column form (main.go:123-138).
+type Cols struct {
+	PID, GPU, Node, SMUtil, MemUtil []uint32
+	Used, TsUs, NodeOff, GPUTotal   []uint64
+}
+
+func (c *Ctx) Ingest(s *Cols) error {
+	var pin runtime.Pinner
+	defer pin.Unpin()
+	for _, a := range [][]uint32{s.PID, s.GPU, s.Node, s.SMUtil, s.MemUtil} {
+		if len(a) > 0 {
+			pin.Pin(&a[0])
+		}
+	}
+	for _, a := range [][]uint64{s.Used, s.TsUs, s.NodeOff, s.GPUTotal} {
+		if len(a) > 0 {
+			pin.Pin(&a[0])
+		}
+	}
+	cc := C.kgx_cols{n: C.uint64_t(len(s.PID)), pid: u32p(s.PID), gpu: u32p(s.GPU), used: u64p(s.Used), node: u32p(s.Node),
+		sm_util: u32p(s.SMUtil), mem_util: u32p(s.MemUtil), ts_us: u64p(s.TsUs), node_off: u64p(s.NodeOff), gpu_total: u64p(s.GPUTotal)}
+	return c.err(C.kgx_ingest(c.p, &cc))
+}
+
+func (c *Ctx) ResetWindow() error { return c.err(C.kgx_reset_window(c.p)) }
+
+// Render returns the text exposition; buf is reused when large enough.
+func (c *Ctx) Render(buf []byte) ([]byte, error) {
+	for {
+		var n C.size_t
+		var p *C.uint8_t
+		if cap(buf) > 0 {
+			p = (*C.uint8_t)(unsafe.Pointer(&buf[:1][0]))
+		}
+		rc := C.kgx_render(c.p, p, C.size_t(cap(buf)), &n)
+		if rc == C.KGX_E_NOSPACE {
+			buf = make([]byte, 0, int(n)+int(n)/8)
+			continue
+		}
+		if err := c.err(rc); err != nil {
+			return nil, err
+		}
+		return buf[:int(n)], nil
+	}
+}
+
+type FamilyInfo struct {
+	Name, Help string
+	LabelNames []string
+}
+
+func (c *Ctx) Families() []FamilyInfo {
+	n := int(C.kgx_family_count(c.p))
+	out := make([]FamilyInfo, n)
+	for f := 0; f < n; f++ {
+		var name, help *C.char
+		var names **C.char
+		var nl C.int
+		C.kgx_family_info(c.p, C.int(f), &name, &help, &names, &nl)
+		out[f] = FamilyInfo{Name: C.GoString(name), Help: C.GoString(help)}
+		for _, p := range unsafe.Slice(names, int(nl)) {
+			out[f].LabelNames = append(out[f].LabelNames, C.GoString(p))
+		}
+	}
+	return out
+}
+
+// ReadValues returns the values and slot ids of one family in exposition order.
+func (c *Ctx) ReadValues(family int) ([]float64, []uint32, error) {
+	var n C.size_t
+	C.kgx_read_values(c.p, C.int(family), nil, nil, 0, &n)
+	vals, slots := make([]float64, int(n)), make([]uint32, int(n))
+	if n == 0 {
+		return vals, slots, nil
+	}
+	rc := C.kgx_read_values(c.p, C.int(family), (*C.double)(unsafe.Pointer(&vals[0])), u32p(slots), n, &n)
+	return vals[:int(n)], slots[:int(n)], c.err(rc)
+}
+
+// SlotLabels returns the pre-escaped `{name="value",...}` text of a slot.
+func (c *Ctx) SlotLabels(slot uint32) string {
+	buf := make([]byte, 1024)
+	var n C.size_t
+	C.kgx_slot_labels(c.p, C.uint32_t(slot), (*C.char)(unsafe.Pointer(&buf[0])), C.size_t(len(buf)), &n)
+	if int(n) > len(buf) {
+		buf = make([]byte, int(n))
+		C.kgx_slot_labels(c.p, C.uint32_t(slot), (*C.char)(unsafe.Pointer(&buf[0])), C.size_t(len(buf)), &n)
+	}
+	return string(buf[:int(n)])
+}
