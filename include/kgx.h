@@ -191,6 +191,32 @@ int kgx_render_device(kgx_ctx* ctx, size_t* len);
  * `cap`.  If cap is too small returns KGX_E_NOSPACE with *len = needed. */
 int kgx_render(kgx_ctx* ctx, uint8_t* out, size_t cap, size_t* len);
 
+/* Render without allocating anything.  (No counterpart in the reference: Go's
+ * promhttp handler allocates freely.  It exists for embedders that cannot call
+ * cudaMalloc when a scrape arrives: the exporter may share its GPU with a job
+ * that has reserved every byte of device memory, and a latency-bound handler
+ * cannot afford the device-wide stall that cudaMalloc/cudaFree bring.)
+ * Same bytes as kgx_render_device, but written into `d_out`, DEVICE memory the
+ * caller owns (16-byte aligned, `cap` bytes), and with the writer's scratch in
+ * a fixed array inside the library image instead of ctx-owned buffers.  That
+ * array takes KGX_NOALLOC_SCRATCH_BYTES on every GPU that loads the library,
+ * for the life of the process.  It makes no cudaMalloc/cudaFree (nor any other
+ * allocating call) and leaves the ctx-owned body of kgx_render untouched.
+ *   - Limits: at most KGX_NOALLOC_MAX_TILES render tiles (a tile is up to 256
+ *     series of one family of one node) and KGX_NOALLOC_MAX_NODES nodes;
+ *     beyond that it returns KGX_E_LIMIT and kgx_render must be used.
+ *   - `cap` must cover the worst-case body size; if it does not (or d_out is
+ *     NULL) it returns KGX_E_NOSPACE with that size in *len.
+ *   - The first call on a GPU looks up the array's device address
+ *     (cudaGetSymbolAddress); make that first call outside any stream capture.
+ *   - All calls, from every ctx on that GPU, share the one array: it is cleared
+ *     at the start of each call, and two calls that overlap on the GPU (two
+ *     ctxs on different streams) race.  Serialise them. */
+#define KGX_NOALLOC_MAX_TILES 16384
+#define KGX_NOALLOC_MAX_NODES 4096
+#define KGX_NOALLOC_SCRATCH_BYTES ((8 + KGX_NOALLOC_MAX_TILES + KGX_NOALLOC_MAX_NODES + 1) * 8) /* 163 912 */
+int kgx_render_noalloc(kgx_ctx* ctx, uint8_t* d_out, size_t cap, size_t* len);
+
 /* Device pointer and size of the last rendered text (valid until the next
  * render on this ctx); for peer copies / NCCL gathers of bodies. */
 int kgx_body_device(kgx_ctx* ctx, const uint8_t** dptr, size_t* len);

@@ -768,3 +768,88 @@ int kgx_profile_reset(kgx_ctx* c) {
 }
 
 }  // extern "C"
+
+// =================== render without any allocation ==========================
+// kgx_render_noalloc: the exposition writer for callers that must not touch the
+// CUDA allocator at scrape time.  Two kinds of embedder are in that position:
+// a /metrics handler that shares its GPU with a training job which has already
+// claimed all device memory (a cudaMalloc there fails, or worse, succeeds and
+// starves the job), and a handler with a latency budget that cannot absorb the
+// device-wide synchronisation cudaMalloc/cudaFree imply.  For them the writer's
+// scratch — the look-back word of every tile, the ticket and length counters,
+// and the per-node body offsets — lives in one fixed array that is part of the
+// library image, and the text goes straight into a device buffer the caller
+// owns.  The array costs KGX_NOALLOC_SCRATCH_BYTES on every GPU that loads the
+// library, until the process exits.
+namespace {
+
+constexpr uint32_t kNoallocMaxTiles = KGX_NOALLOC_MAX_TILES;
+constexpr uint32_t kNoallocMaxNodes = KGX_NOALLOC_MAX_NODES;
+constexpr size_t kNoallocWords = size_t(C_COUNT) + kNoallocMaxTiles + kNoallocMaxNodes + 1;
+static_assert(kNoallocWords * 8 == KGX_NOALLOC_SCRATCH_BYTES, "header and scratch array disagree");
+
+// [0, C_COUNT)            counters (ticket, total length)
+// [C_COUNT, +max tiles)   look-back words
+// [.., +max nodes + 1)    body offset of every node
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[kNoallocWords];
+
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+unsigned long long* g_noalloc_ptr[kMaxDevices] = {};  // device address of the array, per GPU
+
+// The array's name is only a host-side handle here; what a kernel needs is the
+// device address, which differs per GPU.  Looked up once per device, with that
+// device current.
+int noalloc_scratch(kgx_ctx* c, unsigned long long** out) {
+  if (c->device < 0 || c->device >= kMaxDevices) return fail(c, KGX_E_LIMIT, "device index beyond 63");
+  std::lock_guard<std::mutex> g(g_noalloc_mu);
+  if (!g_noalloc_ptr[c->device]) {
+    void* p = nullptr;
+    KGX_CUDA(c, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    g_noalloc_ptr[c->device] = static_cast<unsigned long long*>(p);
+  }
+  *out = g_noalloc_ptr[c->device];
+  return KGX_OK;
+}
+
+}  // namespace
+
+extern "C" int kgx_render_noalloc(kgx_ctx* c, uint8_t* d_out, size_t cap, size_t* len) {
+  if (!c || !len) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_render_noalloc before kgx_set_table");
+  if (c->n_tiles == 0) { *len = 0; return KGX_OK; }
+  if (c->n_tiles > kNoallocMaxTiles)
+    return fail(c, KGX_E_LIMIT, "kgx_render_noalloc: more render tiles than KGX_NOALLOC_MAX_TILES; use kgx_render");
+  if (c->plan.n_nodes > kNoallocMaxNodes)
+    return fail(c, KGX_E_LIMIT, "kgx_render_noalloc: more nodes than KGX_NOALLOC_MAX_NODES; use kgx_render");
+  // the writer does not bounds-check: the buffer must hold the worst case
+  uint64_t bound = 64;
+  for (const FamMeta& m : c->fam)
+    bound += uint64_t(c->n_series) * (m.name_len + 2 + kMaxValueText) + c->lbl_bytes + uint64_t(c->plan.n_nodes) * m.header_len;
+  if (!d_out || cap < bound) { *len = size_t(bound); return fail(c, KGX_E_NOSPACE, "kgx_render_noalloc: output buffer below the worst-case size (returned in *len)"); }
+  if (reinterpret_cast<uintptr_t>(d_out) & 15) return fail(c, KGX_E_INVAL, "kgx_render_noalloc: output buffer must be 16-byte aligned");
+  unsigned long long* scratch = nullptr;
+  KGX_TRY(noalloc_scratch(c, &scratch));
+  // the array still holds the previous call's words: everything the kernel
+  // expects to start from zero (or from "unset") is cleared here
+  KGX_CUDA(c, cudaMemsetAsync(scratch, 0, (size_t(C_COUNT) + c->n_tiles) * 8, c->stream));
+  KGX_CUDA(c, cudaMemsetAsync(scratch + C_COUNT + kNoallocMaxTiles, 0xff, (size_t(c->plan.n_nodes) + 1) * 8, c->stream));
+  DevRender R{};
+  R.fam = ptr<FamMeta>(c->d_fam);
+  R.tiles = ptr<Tile>(c->d_tiles); R.n_tiles = c->n_tiles;
+  R.lbl_off = ptr<unsigned long long>(c->d_lbl_off); R.lbl_blob = ptr<uint8_t>(c->d_lbl_blob);
+  R.ser_gidx = ptr<uint32_t>(c->d_ser_gidx); R.gpu_total = ptr<unsigned long long>(c->d_gpu_total);
+  R.tile_state = scratch + C_COUNT;
+  R.node_body_off = scratch + C_COUNT + kNoallocMaxTiles;
+  R.out = d_out; R.smem_bytes = c->render_smem;
+  const int grid = int(std::min<uint32_t>(c->n_tiles, uint32_t(c->render_grid)));
+  k_render<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, acc_view(c), scratch);
+  c->stats.kernel_launches += 1;
+  KGX_TRY(launch_check(c, "k_render (noalloc)"));
+  KGX_CUDA(c, cudaMemcpyAsync(c->h_counters + C_TICKET + 1, scratch + C_TOTAL_LEN, 8, cudaMemcpyDeviceToHost, c->stream));
+  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  *len = size_t(c->h_counters[C_TICKET + 1]);
+  return KGX_OK;
+}
