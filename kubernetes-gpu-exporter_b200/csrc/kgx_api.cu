@@ -12,6 +12,7 @@
 
 #include "../../include/kgx.h"
 #include "kgx_kernels.cuh"
+#include "kgx_render2.cuh"
 #include "kgx_table.hpp"
 
 using namespace kgx;
@@ -56,6 +57,8 @@ struct kgx_ctx {
   // render
   DBuf d_fam, d_tiles, d_tile_state, d_node_body_off, d_out;
   uint32_t n_tiles = 0, tile_lines = 0, render_smem = 0;
+  bool render_v2 = false;  // second-generation writer (needs metric names of 15..64 bytes)
+  RenderLayout lay{};
   int render_grid = 0;
   size_t last_len = 0;
   bool rendered = false;
@@ -350,17 +353,40 @@ int upload_plan(kgx_ctx* c) {
   KGX_CUDA(c, cudaMemsetAsync(c->d_gpu_total.p, 0, size_t(p.n_nodes) * p.G * 8, c->stream));
   KGX_TRY(dev_reserve(c, c->d_node_body_off, (size_t(p.n_nodes) + 1) * 8));
   KGX_TRY(upload(c, c->d_fam, c->fam.data(), c->fam.size()));
-  // tile geometry: lines per tile so that a whole tile fits the smem buffer
-  uint32_t max_name = 0, max_header = 0;
-  for (const FamMeta& m : c->fam) { max_name = std::max(max_name, m.name_len); max_header = std::max(max_header, m.header_len); }
+  // tile geometry: lines per tile so that a whole tile fits the shared-memory buffers
+  uint32_t max_name = 0, min_name = ~0u, max_header = 0;
+  for (const FamMeta& m : c->fam) {
+    max_name = std::max(max_name, m.name_len); min_name = std::min(min_name, m.name_len);
+    max_header = std::max(max_header, m.header_len);
+  }
   const uint64_t max_line = uint64_t(max_name) + p.max_label_len + 2 + kMaxValueText;
-  const uint64_t budget = 96 * 1024;
-  if (max_line + max_header + 32 > budget) return fail(c, KGX_E_LIMIT, "label text too long for one render tile");
-  c->tile_lines = uint32_t(std::min<uint64_t>(kRenderThreads, (budget - max_header - 32) / max_line));
-  c->render_smem = uint32_t((max_header + uint64_t(c->tile_lines) * max_line + 32 + 15) & ~15ull);
-  KGX_CUDA(c, cudaFuncSetAttribute(k_render, cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->render_smem)));
+  c->render_v2 = min_name >= 15 && max_name <= 64 && c->fam.size() <= size_t(kMaxFamilies) && !getenv("KGX_RENDER_V1");
   int occ = 1;
-  KGX_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_render, kRenderThreads, c->render_smem));
+  if (c->render_v2) {
+    // per line: value slot + staged label + output text; 3 CTAs per SM when labels are short
+    const uint64_t fixed = uint64_t(kMaxFamilies) * kNameStride + 64 + (64 + 16) + (max_header + 64);
+    const uint64_t per_line = kSlotBytes + p.max_label_len + max_line;
+    uint64_t budget = 74 * 1024;
+    if (fixed + 16 * per_line > budget) budget = 200 * 1024;  // long labels: one CTA per SM
+    if (fixed + per_line > budget) return fail(c, KGX_E_LIMIT, "label text too long for one render tile");
+    c->tile_lines = uint32_t(std::min<uint64_t>(kRenderThreads, (budget - fixed) / per_line));
+    auto up16 = [](uint64_t v) { return uint32_t((v + 15) & ~15ull); };
+    c->lay.names = 0;
+    c->lay.slots = up16(uint64_t(kMaxFamilies) * kNameStride);
+    c->lay.stage = up16(c->lay.slots + uint64_t(kRenderThreads) * kSlotBytes + 32);
+    c->lay.out = up16(c->lay.stage + 32 + uint64_t(c->tile_lines) * p.max_label_len + 48);
+    c->lay.total = up16(c->lay.out + 16 + max_header + uint64_t(c->tile_lines) * max_line + 48);
+    c->render_smem = c->lay.total;
+    KGX_CUDA(c, cudaFuncSetAttribute(k_render2, cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->render_smem)));
+    KGX_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_render2, kRenderThreads, c->render_smem));
+  } else {
+    const uint64_t budget = 96 * 1024;
+    if (max_line + max_header + 32 > budget) return fail(c, KGX_E_LIMIT, "label text too long for one render tile");
+    c->tile_lines = uint32_t(std::min<uint64_t>(kRenderThreads, (budget - max_header - 32) / max_line));
+    c->render_smem = uint32_t((max_header + uint64_t(c->tile_lines) * max_line + 32 + 15) & ~15ull);
+    KGX_CUDA(c, cudaFuncSetAttribute(k_render, cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->render_smem)));
+    KGX_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_render, kRenderThreads, c->render_smem));
+  }
   c->render_grid = std::max(1, occ) * c->sm_count;
   KGX_CUDA(c, cudaStreamSynchronize(c->stream));
   return KGX_OK;
@@ -429,7 +455,7 @@ int render_device_locked(kgx_ctx* c, size_t* len) {
     KGX_CUDA(c, cudaMemsetAsync(c->d_node_body_off.p, 0xff, (size_t(c->plan.n_nodes) + 1) * 8, c->stream));
   }
   DevRender R{};
-  R.fam = ptr<FamMeta>(c->d_fam);
+  R.fam = ptr<FamMeta>(c->d_fam); R.n_families = uint32_t(c->fam.size());
   R.tiles = ptr<Tile>(c->d_tiles); R.n_tiles = c->n_tiles;
   R.lbl_off = ptr<unsigned long long>(c->d_lbl_off); R.lbl_blob = ptr<uint8_t>(c->d_lbl_blob);
   R.ser_gidx = ptr<uint32_t>(c->d_ser_gidx); R.gpu_total = ptr<unsigned long long>(c->d_gpu_total);
@@ -438,7 +464,8 @@ int render_device_locked(kgx_ctx* c, size_t* len) {
   {
     Timed tm(c, KGX_K_RENDER);
     const int grid = int(std::min<uint32_t>(c->n_tiles, uint32_t(c->render_grid)));
-    k_render<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, acc_view(c), ctr);
+    if (c->render_v2) k_render2<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), ctr);
+    else k_render<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, acc_view(c), ctr);
     tm.launches(1);
     KGX_TRY(launch_check(c, "k_render"));
   }
@@ -837,7 +864,7 @@ extern "C" int kgx_render_noalloc(kgx_ctx* c, uint8_t* d_out, size_t cap, size_t
   KGX_CUDA(c, cudaMemsetAsync(scratch, 0, (size_t(C_COUNT) + c->n_tiles) * 8, c->stream));
   KGX_CUDA(c, cudaMemsetAsync(scratch + C_COUNT + kNoallocMaxTiles, 0xff, (size_t(c->plan.n_nodes) + 1) * 8, c->stream));
   DevRender R{};
-  R.fam = ptr<FamMeta>(c->d_fam);
+  R.fam = ptr<FamMeta>(c->d_fam); R.n_families = uint32_t(c->fam.size());
   R.tiles = ptr<Tile>(c->d_tiles); R.n_tiles = c->n_tiles;
   R.lbl_off = ptr<unsigned long long>(c->d_lbl_off); R.lbl_blob = ptr<uint8_t>(c->d_lbl_blob);
   R.ser_gidx = ptr<uint32_t>(c->d_ser_gidx); R.gpu_total = ptr<unsigned long long>(c->d_gpu_total);
@@ -845,7 +872,8 @@ extern "C" int kgx_render_noalloc(kgx_ctx* c, uint8_t* d_out, size_t cap, size_t
   R.node_body_off = scratch + C_COUNT + kNoallocMaxTiles;
   R.out = d_out; R.smem_bytes = c->render_smem;
   const int grid = int(std::min<uint32_t>(c->n_tiles, uint32_t(c->render_grid)));
-  k_render<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, acc_view(c), scratch);
+  if (c->render_v2) k_render2<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), scratch);
+  else k_render<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, acc_view(c), scratch);
   c->stats.kernel_launches += 1;
   KGX_TRY(launch_check(c, "k_render (noalloc)"));
   KGX_CUDA(c, cudaMemcpyAsync(c->h_counters + C_TICKET + 1, scratch + C_TOTAL_LEN, 8, cudaMemcpyDeviceToHost, c->stream));

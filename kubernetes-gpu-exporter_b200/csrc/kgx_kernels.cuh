@@ -327,6 +327,7 @@ struct Tile {
 
 struct DevRender {
   const FamMeta* fam;  // [n_families], device global memory (one schema per ctx)
+  uint32_t n_families;
   const Tile* tiles;
   uint32_t n_tiles;
   const unsigned long long* lbl_off;  // [n_series+1]

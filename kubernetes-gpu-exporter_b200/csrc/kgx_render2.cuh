@@ -1,0 +1,229 @@
+// kgx_render2.cuh — exposition writer, second generation (sm_100a).
+//
+// Same contract as k_render (byte-identical output; replaces what main.go:69-71
+// serves through Registry.Gather + expfmt), rebuilt around how the bytes move:
+//
+//   * the label text of a tile is ONE contiguous byte range of the series label
+//     blob: a single TMA bulk copy (cp.async.bulk global->shared, completion on
+//     an mbarrier) stages it while the threads format their values;
+//   * each thread owns one line and formats its value once, straight into a
+//     shared-memory slot (" <value>\n");
+//   * line lengths -> CTA scan -> inter-tile decoupled look-back give every
+//     line its exact byte offset;
+//   * each thread then streams its line into the shared output buffer as
+//     16-byte chunks ALIGNED TO THE GLOBAL ADDRESS: a chunk belongs to the line
+//     that holds its first byte, so every store is a full STS.128 and no two
+//     threads touch the same chunk.  Sources (metric name, staged labels, value
+//     slot, the next line's name prefix) are read with word loads + funnel
+//     shifts; only the 2-3 chunks that straddle two sources need a byte merge;
+//   * the finished tile leaves with one TMA bulk store (shared->global); the
+//     few bytes before/after the 16-byte-aligned body go out as byte stores.
+#pragma once
+#include "kgx_kernels.cuh"
+
+namespace kgx {
+
+struct RenderLayout {  // byte offsets inside dynamic shared memory (all 16-aligned)
+  uint32_t names;      // kMaxFamilies x 96: [16 pad][name (<=64)][16 pad]
+  uint32_t slots;      // tile_lines x 28: " <value>\n"
+  uint32_t stage;      // staged label text (+32 slack either side)
+  uint32_t out;        // the tile's output text
+  uint32_t total;
+};
+constexpr uint32_t kSlotBytes = 28;  // 7 words: odd word stride -> conflict-free byte stores
+constexpr uint32_t kNameStride = 96;
+
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint4 v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+// 16 bytes starting at shared byte address `a` (any alignment)
+__device__ __forceinline__ uint4 gather16(uint32_t a) {
+  const uint32_t b = a & ~3u, r = (a & 3u) * 8u;
+  const uint32_t w0 = lds32(b), w1 = lds32(b + 4), w2 = lds32(b + 8), w3 = lds32(b + 12), w4 = lds32(b + 16);
+  return make_uint4(__funnelshift_r(w0, w1, r), __funnelshift_r(w1, w2, r), __funnelshift_r(w2, w3, r),
+                    __funnelshift_r(w3, w4, r));
+}
+// bytes [0,e) from lo, bytes [e,16) from hi   (0 < e < 16)
+__device__ __forceinline__ uint4 merge16(uint4 lo, uint4 hi, uint32_t e) {
+  auto m = [e](uint32_t w) -> uint32_t {  // mask of the bytes of word w that are < e
+    const int n = int(e) - int(4 * w);
+    return n <= 0 ? 0u : (n >= 4 ? 0xffffffffu : ((1u << (8 * n)) - 1u));
+  };
+  const uint32_t m0 = m(0), m1 = m(1), m2 = m(2), m3 = m(3);
+  return make_uint4((lo.x & m0) | (hi.x & ~m0), (lo.y & m1) | (hi.y & ~m1), (lo.z & m2) | (hi.z & ~m2),
+                    (lo.w & m3) | (hi.w & ~m3));
+}
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+// TMA bulk copy global -> shared, completion counted on the mbarrier
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+// TMA bulk copy shared -> global
+__device__ __forceinline__ void bulk_s2g(void* dst, uint32_t src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
+}
+
+__global__ void __launch_bounds__(kRenderThreads) k_render2(DevRender R, RenderLayout lay, DevAcc acc, unsigned long long* counters) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ unsigned long long s_scan[kRenderThreads / 32];
+  __shared__ uint32_t s_tile;
+  __shared__ unsigned long long s_base;
+  __shared__ __align__(8) unsigned long long s_bar;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const uint32_t sm0 = uint32_t(__cvta_generic_to_shared(smem));
+  const uint32_t bar = uint32_t(__cvta_generic_to_shared(&s_bar));
+  // one-time: metric names of every family, with slack on both sides
+  for (uint32_t i = tid; i < kMaxFamilies * kNameStride; i += kRenderThreads) {
+    const uint32_t f = i / kNameStride, o = i % kNameStride;
+    smem[lay.names + i] = (o >= 16 && o < 16 + 64 && f < R.n_families) ? R.fam[f].name[o - 16] : uint8_t('#');
+  }
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  uint32_t parity = 0;
+  for (;;) {
+    if (tid == 0) s_tile = uint32_t(atomicAdd(&counters[C_TICKET], 1ull));
+    __syncthreads();
+    const uint32_t t = s_tile;
+    if (t >= R.n_tiles) {
+      if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // my bulk stores have fully landed
+      return;
+    }
+    const Tile tile = R.tiles[t];
+    const FamMeta& fm = R.fam[tile.family];
+    const uint32_t name_len = fm.name_len;
+    // ---- stage the tile's label text: one bulk copy of an aligned superset
+    const unsigned long long L0 = R.lbl_off[tile.first];
+    const unsigned long long g0 = L0 & ~15ull;
+    if (tid == 0) {
+      const unsigned long long L1 = R.lbl_off[tile.first + tile.count];
+      const uint32_t bytes = uint32_t(((L1 + 15ull) & ~15ull) - g0);
+      if (bytes) {
+        mbar_expect_tx(bar, bytes);
+        bulk_g2s(sm0 + lay.stage + 32, R.lbl_blob + g0, bytes, bar);
+      } else {
+        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+      }
+    }
+    // ---- pass 1: value text and exact length of my line
+    const uint32_t slot = sm0 + lay.slots + tid * kSlotBytes;
+    uint32_t len = 0, lbl_len = 0, vlen = 0, lbl_src = 0;
+    bool live = false;
+    if (tid < tile.count) {
+      const uint32_t r = tile.first + tid;
+      const double v = series_value(fm.kind, acc, R, r, live);
+      if (live) {
+        uint8_t* sp = smem + lay.slots + tid * kSlotBytes;
+        sp[0] = ' ';
+        vlen = uint32_t(format_value(v, sp + 1));
+        sp[1 + vlen] = '\n';
+        const unsigned long long at = R.lbl_off[r];
+        lbl_len = uint32_t(R.lbl_off[r + 1] - at);
+        lbl_src = sm0 + lay.stage + 32 + uint32_t(at - g0);
+        len = name_len + lbl_len + vlen + 2;
+      }
+    }
+    const uint32_t hdr = ((tile.flags & 1) && acc.node_live[tile.node] != 0) ? fm.header_len : 0;
+    // ---- exclusive scan over the CTA: low word = bytes, high word = live lines
+    const unsigned long long mine = (uint64_t(live) << 32) | len;
+    unsigned long long inc = mine;
+    for (int o = 1; o < 32; o <<= 1) { unsigned long long u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
+    if (lane == 31) s_scan[wid] = inc;
+    __syncthreads();
+    unsigned long long woff = 0, all = 0;
+    for (int k = 0; k < kRenderThreads / 32; ++k) { if (k < int(wid)) woff += s_scan[k]; all += s_scan[k]; }
+    const unsigned long long exc = woff + inc - mine;
+    const uint32_t off = hdr + uint32_t(exc);
+    const uint32_t total = hdr + uint32_t(all);
+    const bool first_live = live && uint32_t(exc >> 32) == 0;
+    const bool last_live = live && uint32_t(exc >> 32) + 1 == uint32_t(all >> 32);
+    // ---- inter-tile offset: decoupled look-back over the tile chain
+    if (tid == 0) {
+      unsigned long long base = 0;
+      if (t > 0) {
+        atomicExch(&R.tile_state[t], kStAgg | total);
+        for (uint32_t p = t; p-- > 0;) {
+          unsigned long long s;
+          do { s = *(volatile unsigned long long*)&R.tile_state[p]; } while ((s & kStMask) == 0);
+          base += s & ~kStMask;
+          if ((s & kStMask) == kStPrefix) break;
+        }
+      }
+      atomicExch(&R.tile_state[t], kStPrefix | (base + total));
+      s_base = base;
+      if (tile.flags & 2) R.node_body_off[tile.node] = base;
+      if (t == R.n_tiles - 1) counters[C_TOTAL_LEN] = base + total;
+    }
+    __syncthreads();
+    const unsigned long long base = s_base;
+    const uint32_t sh = uint32_t(base & 15);   // shared offset == global address (mod 16)
+    const uint32_t outb = sm0 + lay.out;       // byte p of the tile lives at outb + sh + p
+    mbar_wait(bar, parity);                    // staged labels have landed
+    parity ^= 1;
+    // ---- pass 2: stream my line into the output buffer as aligned 16-byte chunks
+    if (live) {
+      const uint32_t g = outb + sh + off;                    // first byte of my line
+      const uint32_t b0 = g + name_len, b1 = b0 + lbl_len, b2 = b1 + vlen + 2;  // source boundaries; b2 = line end
+      const uint32_t start = first_live ? (g & ~15u) : ((g + 15u) & ~15u);
+      const uint32_t stop = (b2 + 15u) & ~15u;               // my chunks: [start, stop)
+      const uint32_t name_sm = sm0 + lay.names + tile.family * kNameStride + 16;
+      const uint32_t d0 = name_sm - g, d1 = lbl_src - b0, d2 = slot - b1, d3 = name_sm - b2;  // source = position + delta
+      (void)last_live;  // after the last line the chunk tail is slack: never copied out
+      for (uint32_t p = start; p < stop; p += 16) {
+        const uint32_t d = p >= b2 ? d3 : (p >= b1 ? d2 : (p >= b0 ? d1 : d0));
+        uint4 o = gather16(p + d);
+        if (b0 > p && b0 < p + 16) o = merge16(o, gather16(p + d1), b0 - p);
+        if (b1 > p && b1 < p + 16) o = merge16(o, gather16(p + d2), b1 - p);
+        if (b2 > p && b2 < p + 16) o = merge16(o, gather16(p + d3), b2 - p);
+        sts128(p, o);
+      }
+    }
+    if (hdr) {  // the header goes in after the lines: the first line's leading chunk overlaps its tail
+      __syncthreads();
+      for (uint32_t i = tid; i < hdr; i += kRenderThreads) smem[lay.out + sh + i] = fm.header[i];
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // my generic-proxy writes -> visible to the bulk store
+    __syncthreads();
+    // ---- the tile leaves: byte head, bulk body, byte tail
+    uint8_t* gout = R.out + base;
+    const uint32_t head = min(total, (16u - sh) & 15u);
+    const uint32_t body = (total - head) & ~15u;
+    if (tid == 0 && body) {
+      bulk_s2g(gout + head, outb + sh + head, body);
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    }
+    if (tid >= 32 && tid < 32 + head) gout[tid - 32] = smem[lay.out + sh + tid - 32];
+    if (tid >= 64 && tid < 64 + (total - head - body)) {
+      const uint32_t i = head + body + tid - 64;
+      gout[i] = smem[lay.out + sh + i];
+    }
+    if (tid == 0 && body) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    __syncthreads();  // the buffers are free again
+  }
+}
+
+}  // namespace kgx
