@@ -364,7 +364,7 @@ int upload_plan(kgx_ctx* c) {
   int occ = 1;
   if (c->render_v2) {
     // per line: value slot + staged label + output text; 3 CTAs per SM when labels are short
-    const uint64_t fixed = uint64_t(kMaxFamilies) * kNameStride + 64 + (64 + 16) + (max_header + 64);
+    const uint64_t fixed = uint64_t(kMaxFamilies) * kNameStride + 64 + (64 + 16 + 128) + (max_header + 64);
     const uint64_t per_line = kSlotBytes + p.max_label_len + max_line;
     uint64_t budget = 74 * 1024;
     if (fixed + 16 * per_line > budget) budget = 200 * 1024;  // long labels: one CTA per SM
@@ -374,7 +374,7 @@ int upload_plan(kgx_ctx* c) {
     c->lay.names = 0;
     c->lay.slots = up16(uint64_t(kMaxFamilies) * kNameStride);
     c->lay.stage = up16(c->lay.slots + uint64_t(kRenderThreads) * kSlotBytes + 32);
-    c->lay.out = up16(c->lay.stage + 32 + uint64_t(c->tile_lines) * p.max_label_len + 48);
+    c->lay.out = up16(c->lay.stage + 32 + uint64_t(c->tile_lines) * p.max_label_len + 128 + 48);
     c->lay.total = up16(c->lay.out + 16 + max_header + uint64_t(c->tile_lines) * max_line + 48);
     c->render_smem = c->lay.total;
     KGX_CUDA(c, cudaFuncSetAttribute(k_render2, cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->render_smem)));

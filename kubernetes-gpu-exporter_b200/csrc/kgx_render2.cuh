@@ -48,15 +48,13 @@ __device__ __forceinline__ uint4 gather16(uint32_t a) {
   return make_uint4(__funnelshift_r(w0, w1, r), __funnelshift_r(w1, w2, r), __funnelshift_r(w2, w3, r),
                     __funnelshift_r(w3, w4, r));
 }
-// bytes [0,e) from lo, bytes [e,16) from hi   (0 < e < 16)
-__device__ __forceinline__ uint4 merge16(uint4 lo, uint4 hi, uint32_t e) {
-  auto m = [e](uint32_t w) -> uint32_t {  // mask of the bytes of word w that are < e
-    const int n = int(e) - int(4 * w);
-    return n <= 0 ? 0u : (n >= 4 ? 0xffffffffu : ((1u << (8 * n)) - 1u));
-  };
-  const uint32_t m0 = m(0), m1 = m(1), m2 = m(2), m3 = m(3);
-  return make_uint4((lo.x & m0) | (hi.x & ~m0), (lo.y & m1) | (hi.y & ~m1), (lo.z & m2) | (hi.z & ~m2),
-                    (lo.w & m3) | (hi.w & ~m3));
+// bytes [0,e) from lo, bytes [e,16) from hi (0 < e < 16); mask_sm: shared table of
+// 16 byte masks, entry e = the first e bytes set
+__device__ __forceinline__ uint4 merge16(uint4 lo, uint4 hi, uint32_t e, uint32_t mask_sm) {
+  uint4 m;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(m.x), "=r"(m.y), "=r"(m.z), "=r"(m.w) : "r"(mask_sm + 16u * e));
+  return make_uint4((lo.x & m.x) | (hi.x & ~m.x), (lo.y & m.y) | (hi.y & ~m.y), (lo.z & m.z) | (hi.z & ~m.z),
+                    (lo.w & m.w) | (hi.w & ~m.w));
 }
 
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -91,6 +89,7 @@ __global__ void __launch_bounds__(kRenderThreads) k_render2(DevRender R, RenderL
   __shared__ uint32_t s_tile;
   __shared__ unsigned long long s_base;
   __shared__ __align__(8) unsigned long long s_bar;
+  __shared__ __align__(16) uint32_t s_mask[16][4];
   const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const uint32_t sm0 = uint32_t(__cvta_generic_to_shared(smem));
   const uint32_t bar = uint32_t(__cvta_generic_to_shared(&s_bar));
@@ -99,6 +98,12 @@ __global__ void __launch_bounds__(kRenderThreads) k_render2(DevRender R, RenderL
     const uint32_t f = i / kNameStride, o = i % kNameStride;
     smem[lay.names + i] = (o >= 16 && o < 16 + 64 && f < R.n_families) ? R.fam[f].name[o - 16] : uint8_t('#');
   }
+  if (tid < 64) {  // byte-mask table for merge16: entry e has the first e bytes set
+    const uint32_t e = tid >> 2, w = tid & 3;
+    const int n = int(e) - int(4 * w);
+    s_mask[e][w] = n <= 0 ? 0u : (n >= 4 ? 0xffffffffu : ((1u << (8 * n)) - 1u));
+  }
+  const uint32_t mask_sm = uint32_t(__cvta_generic_to_shared(&s_mask[0][0]));
   if (tid == 0) {
     mbar_init(bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -118,7 +123,7 @@ __global__ void __launch_bounds__(kRenderThreads) k_render2(DevRender R, RenderL
     const uint32_t name_len = fm.name_len;
     // ---- stage the tile's label text: one bulk copy of an aligned superset
     const unsigned long long L0 = R.lbl_off[tile.first];
-    const unsigned long long g0 = L0 & ~15ull;
+    const unsigned long long g0 = L0 & ~127ull;  // whole 128-byte lines: the copy engine's natural unit
     if (tid == 0) {
       const unsigned long long L1 = R.lbl_off[tile.first + tile.count];
       const uint32_t bytes = uint32_t(((L1 + 15ull) & ~15ull) - g0);
@@ -193,14 +198,27 @@ __global__ void __launch_bounds__(kRenderThreads) k_render2(DevRender R, RenderL
       const uint32_t name_sm = sm0 + lay.names + tile.family * kNameStride + 16;
       const uint32_t d0 = name_sm - g, d1 = lbl_src - b0, d2 = slot - b1, d3 = name_sm - b2;  // source = position + delta
       (void)last_live;  // after the last line the chunk tail is slack: never copied out
-      for (uint32_t p = start; p < stop; p += 16) {
-        const uint32_t d = p >= b2 ? d3 : (p >= b1 ? d2 : (p >= b0 ? d1 : d0));
-        uint4 o = gather16(p + d);
-        if (b0 > p && b0 < p + 16) o = merge16(o, gather16(p + d1), b0 - p);
-        if (b1 > p && b1 < p + 16) o = merge16(o, gather16(p + d2), b1 - p);
-        if (b2 > p && b2 < p + 16) o = merge16(o, gather16(p + d3), b2 - p);
-        sts128(p, o);
-      }
+      // The four sources are appended one after the other, so that all lanes of
+      // a warp are in the same source at the same time (no per-chunk branching
+      // on where the boundaries fall): `acc` holds the chunk at p, of which the
+      // first `e` bytes are already final.
+      uint32_t p = start, e = 0;
+      uint4 a4 = make_uint4(0, 0, 0, 0);
+      auto append = [&](uint32_t d, uint32_t b) {  // source = position + d, up to position b (exclusive)
+        const uint4 nw = gather16(p + d);
+        a4 = e ? merge16(a4, nw, e, mask_sm) : nw;
+        if (b >= p + 16) {
+          sts128(p, a4);
+          p += 16;
+          while (p + 16 <= b) { sts128(p, gather16(p + d)); p += 16; }
+          a4 = gather16(p + d);
+        }
+        e = b - p;
+      };
+      append(d0, b0);
+      append(d1, b1);
+      append(d2, b2);
+      append(d3, stop);
     }
     if (hdr) {  // the header goes in after the lines: the first line's leading chunk overlaps its tail
       __syncthreads();
