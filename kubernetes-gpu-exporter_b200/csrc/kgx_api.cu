@@ -59,7 +59,7 @@ struct kgx_ctx {
   uint32_t n_tiles = 0, tile_lines = 0, render_smem = 0;
   bool render_v2 = false;  // second-generation writer (needs metric names of 15..64 bytes)
   RenderLayout lay{};
-  int render_grid = 0;
+  int render_grid = 0, render_threads = 256;
   size_t last_len = 0;
   bool rendered = false;
   std::vector<FamMeta> fam;
@@ -169,6 +169,22 @@ DevAcc acc_view(kgx_ctx* c) {
   return a;
 }
 int n_acc_arrays(const kgx_ctx* c) { return c->mode == KGX_MODE_X ? 6 : 3; }
+
+// the writer is compiled for three CTA sizes (= lines per tile)
+const void* render2_func(int threads) {
+  switch (threads) {
+    case 64: return reinterpret_cast<const void*>(&k_render2<64>);
+    case 128: return reinterpret_cast<const void*>(&k_render2<128>);
+    default: return reinterpret_cast<const void*>(&k_render2<256>);
+  }
+}
+void launch_render2(kgx_ctx* c, int grid, const DevRender& R, unsigned long long* counters) {
+  switch (c->render_threads) {
+    case 64: k_render2<64><<<grid, 64, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+    case 128: k_render2<128><<<grid, 128, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+    default: k_render2<256><<<grid, 256, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+  }
+}
 
 DevLabels labels_view(kgx_ctx* c) {
   DevLabels L{};
@@ -369,16 +385,18 @@ int upload_plan(kgx_ctx* c) {
     uint64_t budget = 74 * 1024;
     if (fixed + 16 * per_line > budget) budget = 200 * 1024;  // long labels: one CTA per SM
     if (fixed + per_line > budget) return fail(c, KGX_E_LIMIT, "label text too long for one render tile");
-    c->tile_lines = uint32_t(std::min<uint64_t>(kRenderThreads, (budget - fixed) / per_line));
+    if (const char* e = getenv("KGX_RENDER_THREADS")) c->render_threads = atoi(e);
+    if (c->render_threads != 64 && c->render_threads != 128 && c->render_threads != 256) c->render_threads = 256;
+    c->tile_lines = uint32_t(std::min<uint64_t>(uint64_t(c->render_threads), (budget - fixed) / per_line));
     auto up16 = [](uint64_t v) { return uint32_t((v + 15) & ~15ull); };
     c->lay.names = 0;
     c->lay.slots = up16(uint64_t(kMaxFamilies) * kNameStride);
-    c->lay.stage = up16(c->lay.slots + uint64_t(kRenderThreads) * kSlotBytes + 32);
+    c->lay.stage = up16(c->lay.slots + uint64_t(c->render_threads) * kSlotBytes + 32);
     c->lay.out = up16(c->lay.stage + 32 + uint64_t(c->tile_lines) * p.max_label_len + 128 + 48);
     c->lay.total = up16(c->lay.out + 16 + max_header + uint64_t(c->tile_lines) * max_line + 48);
     c->render_smem = c->lay.total;
-    KGX_CUDA(c, cudaFuncSetAttribute(k_render2, cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->render_smem)));
-    KGX_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_render2, kRenderThreads, c->render_smem));
+    KGX_CUDA(c, cudaFuncSetAttribute(render2_func(c->render_threads), cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->render_smem)));
+    KGX_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, render2_func(c->render_threads), c->render_threads, c->render_smem));
   } else {
     const uint64_t budget = 96 * 1024;
     if (max_line + max_header + 32 > budget) return fail(c, KGX_E_LIMIT, "label text too long for one render tile");
@@ -461,10 +479,11 @@ int render_device_locked(kgx_ctx* c, size_t* len) {
   R.ser_gidx = ptr<uint32_t>(c->d_ser_gidx); R.gpu_total = ptr<unsigned long long>(c->d_gpu_total);
   R.tile_state = ptr<unsigned long long>(c->d_tile_state); R.node_body_off = ptr<unsigned long long>(c->d_node_body_off);
   R.out = ptr<uint8_t>(c->d_out); R.smem_bytes = c->render_smem;
+  R.flags = (getenv("KGX_RENDER_TMA_STORE") ? 1u : 0u) | (getenv("KGX_RENDER_LDGSTS") ? 2u : 0u);
   {
     Timed tm(c, KGX_K_RENDER);
     const int grid = int(std::min<uint32_t>(c->n_tiles, uint32_t(c->render_grid)));
-    if (c->render_v2) k_render2<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), ctr);
+    if (c->render_v2) launch_render2(c, grid, R, ctr);
     else k_render<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, acc_view(c), ctr);
     tm.launches(1);
     KGX_TRY(launch_check(c, "k_render"));
@@ -872,7 +891,7 @@ extern "C" int kgx_render_noalloc(kgx_ctx* c, uint8_t* d_out, size_t cap, size_t
   R.node_body_off = scratch + C_COUNT + kNoallocMaxTiles;
   R.out = d_out; R.smem_bytes = c->render_smem;
   const int grid = int(std::min<uint32_t>(c->n_tiles, uint32_t(c->render_grid)));
-  if (c->render_v2) k_render2<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), scratch);
+  if (c->render_v2) launch_render2(c, grid, R, scratch);
   else k_render<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, acc_view(c), scratch);
   c->stats.kernel_launches += 1;
   KGX_TRY(launch_check(c, "k_render (noalloc)"));

@@ -83,9 +83,10 @@ __device__ __forceinline__ void bulk_s2g(void* dst, uint32_t src, uint32_t bytes
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
 }
 
-__global__ void __launch_bounds__(kRenderThreads) k_render2(DevRender R, RenderLayout lay, DevAcc acc, unsigned long long* counters) {
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS) k_render2(DevRender R, RenderLayout lay, DevAcc acc, unsigned long long* counters) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ unsigned long long s_scan[kRenderThreads / 32];
+  __shared__ unsigned long long s_scan[THREADS / 32];
   __shared__ uint32_t s_tile;
   __shared__ unsigned long long s_base;
   __shared__ __align__(8) unsigned long long s_bar;
@@ -94,7 +95,7 @@ __global__ void __launch_bounds__(kRenderThreads) k_render2(DevRender R, RenderL
   const uint32_t sm0 = uint32_t(__cvta_generic_to_shared(smem));
   const uint32_t bar = uint32_t(__cvta_generic_to_shared(&s_bar));
   // one-time: metric names of every family, with slack on both sides
-  for (uint32_t i = tid; i < kMaxFamilies * kNameStride; i += kRenderThreads) {
+  for (uint32_t i = tid; i < kMaxFamilies * kNameStride; i += THREADS) {
     const uint32_t f = i / kNameStride, o = i % kNameStride;
     smem[lay.names + i] = (o >= 16 && o < 16 + 64 && f < R.n_families) ? R.fam[f].name[o - 16] : uint8_t('#');
   }
@@ -124,7 +125,14 @@ __global__ void __launch_bounds__(kRenderThreads) k_render2(DevRender R, RenderL
     // ---- stage the tile's label text: one bulk copy of an aligned superset
     const unsigned long long L0 = R.lbl_off[tile.first];
     const unsigned long long g0 = L0 & ~127ull;  // whole 128-byte lines: the copy engine's natural unit
-    if (tid == 0) {
+    if (R.flags & 2) {  // staged by every thread with 16-byte cp.async (LDGSTS) instead of the TMA engine
+      const unsigned long long L1 = R.lbl_off[tile.first + tile.count];
+      const uint32_t chunks = uint32_t(((L1 + 15ull) & ~15ull) - g0) >> 4;
+      const uint8_t* src = R.lbl_blob + g0;
+      for (uint32_t i = tid; i < chunks; i += THREADS)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sm0 + lay.stage + 32 + 16 * i), "l"(src + 16 * size_t(i)) : "memory");
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    } else if (tid == 0) {
       const unsigned long long L1 = R.lbl_off[tile.first + tile.count];
       const uint32_t bytes = uint32_t(((L1 + 15ull) & ~15ull) - g0);
       if (bytes) {
@@ -160,35 +168,48 @@ __global__ void __launch_bounds__(kRenderThreads) k_render2(DevRender R, RenderL
     if (lane == 31) s_scan[wid] = inc;
     __syncthreads();
     unsigned long long woff = 0, all = 0;
-    for (int k = 0; k < kRenderThreads / 32; ++k) { if (k < int(wid)) woff += s_scan[k]; all += s_scan[k]; }
+    for (int k = 0; k < THREADS / 32; ++k) { if (k < int(wid)) woff += s_scan[k]; all += s_scan[k]; }
     const unsigned long long exc = woff + inc - mine;
     const uint32_t off = hdr + uint32_t(exc);
     const uint32_t total = hdr + uint32_t(all);
     const bool first_live = live && uint32_t(exc >> 32) == 0;
     const bool last_live = live && uint32_t(exc >> 32) + 1 == uint32_t(all >> 32);
     // ---- inter-tile offset: decoupled look-back over the tile chain
-    if (tid == 0) {
+    // Warp 0 inspects 32 predecessors per step: everything after the nearest tile
+    // that already knows its inclusive prefix contributes its own size.
+    if (wid == 0) {
       unsigned long long base = 0;
       if (t > 0) {
-        atomicExch(&R.tile_state[t], kStAgg | total);
-        for (uint32_t p = t; p-- > 0;) {
-          unsigned long long s;
-          do { s = *(volatile unsigned long long*)&R.tile_state[p]; } while ((s & kStMask) == 0);
-          base += s & ~kStMask;
-          if ((s & kStMask) == kStPrefix) break;
+        if (lane == 0) atomicExch(&R.tile_state[t], kStAgg | total);
+        long long p = (long long)t - 1 - lane;  // lane 0 looks at the direct predecessor
+        for (;;) {
+          unsigned long long s = kStPrefix;     // before tile 0: an inclusive prefix of zero
+          if (p >= 0) {
+            do { s = *(volatile unsigned long long*)&R.tile_state[p]; } while ((s & kStMask) == 0);
+          }
+          const uint32_t pfx = __ballot_sync(0xffffffffu, (s & kStMask) == kStPrefix);
+          const uint32_t first = pfx ? uint32_t(__ffs(pfx) - 1) : 32u;
+          unsigned long long v = lane <= first ? (s & ~kStMask) : 0ull;
+          for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+          base += v;
+          if (pfx) break;
+          p -= 32;
         }
       }
-      atomicExch(&R.tile_state[t], kStPrefix | (base + total));
-      s_base = base;
-      if (tile.flags & 2) R.node_body_off[tile.node] = base;
-      if (t == R.n_tiles - 1) counters[C_TOTAL_LEN] = base + total;
+      if (lane == 0) {
+        atomicExch(&R.tile_state[t], kStPrefix | (base + total));
+        s_base = base;
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // previous tile's bulk store has read the output buffer
+        if (tile.flags & 2) R.node_body_off[tile.node] = base;
+        if (t == R.n_tiles - 1) counters[C_TOTAL_LEN] = base + total;
+      }
     }
+    if (R.flags & 2) asm volatile("cp.async.wait_group 0;" ::: "memory");  // my share of the label copy has landed
     __syncthreads();
     const unsigned long long base = s_base;
     const uint32_t sh = uint32_t(base & 15);   // shared offset == global address (mod 16)
     const uint32_t outb = sm0 + lay.out;       // byte p of the tile lives at outb + sh + p
-    mbar_wait(bar, parity);                    // staged labels have landed
-    parity ^= 1;
+    if (!(R.flags & 2)) { mbar_wait(bar, parity); parity ^= 1; }  // staged labels have landed
     // ---- pass 2: stream my line into the output buffer as aligned 16-byte chunks
     if (live) {
       const uint32_t g = outb + sh + off;                    // first byte of my line
@@ -222,25 +243,31 @@ __global__ void __launch_bounds__(kRenderThreads) k_render2(DevRender R, RenderL
     }
     if (hdr) {  // the header goes in after the lines: the first line's leading chunk overlaps its tail
       __syncthreads();
-      for (uint32_t i = tid; i < hdr; i += kRenderThreads) smem[lay.out + sh + i] = fm.header[i];
+      for (uint32_t i = tid; i < hdr; i += THREADS) smem[lay.out + sh + i] = fm.header[i];
     }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // my generic-proxy writes -> visible to the bulk store
+    if (R.flags & 1) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the bulk store
     __syncthreads();
     // ---- the tile leaves: byte head, bulk body, byte tail
     uint8_t* gout = R.out + base;
     const uint32_t head = min(total, (16u - sh) & 15u);
     const uint32_t body = (total - head) & ~15u;
-    if (tid == 0 && body) {
-      bulk_s2g(gout + head, outb + sh + head, body);
-      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    if (R.flags & 1) {  // body through the TMA engine (one bulk store)
+      if (tid == 0 && body) {
+        bulk_s2g(gout + head, outb + sh + head, body);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+    } else {            // body through the LSU: 16 bytes per lane, fully coalesced
+      const uint4* sb = reinterpret_cast<const uint4*>(smem + lay.out + sh + head);
+      uint4* gb = reinterpret_cast<uint4*>(gout + head);
+      for (uint32_t i = tid; i < body / 16; i += THREADS) __stcs(gb + i, sb[i]);
     }
-    if (tid >= 32 && tid < 32 + head) gout[tid - 32] = smem[lay.out + sh + tid - 32];
-    if (tid >= 64 && tid < 64 + (total - head - body)) {
-      const uint32_t i = head + body + tid - 64;
+    if (tid < head) gout[tid] = smem[lay.out + sh + tid];
+    if (tid >= 16 && tid < 16 + (total - head - body)) {
+      const uint32_t i = head + body + tid - 16;
       gout[i] = smem[lay.out + sh + i];
     }
-    if (tid == 0 && body) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-    __syncthreads();  // the buffers are free again
+    // no barrier here: the next tile's first barriers order everything, and the bulk
+    // store's reads of the output buffer are awaited right before it is rewritten
   }
 }
 
