@@ -13,6 +13,7 @@
 #include "../../include/kgx.h"
 #include "kgx_kernels.cuh"
 #include "kgx_render2.cuh"
+#include "kgx_ingest2.cuh"
 #include "kgx_table.hpp"
 
 using namespace kgx;
@@ -40,7 +41,8 @@ struct kgx_ctx {
   bool have_table = false;
   Plan plan;
   // table
-  DBuf d_node_tab, d_tab, d_pk_slot0, d_pk_stride, d_grank, d_node_slot_base;
+  DBuf d_node_tab, d_tab, d_pk_slot0, d_pk_stride, d_grank, d_node_slot_base, d_node_a_base;
+  uint32_t ingest_smem = 0, ingest_cells = 0, ingest_pks = 0;  // staging buffer of the node-grouped join
   DBuf d_A_blob, d_B_blob, d_G_blob, d_A_off, d_B_off, d_G_off, d_runs;
   // index
   DBuf d_bm, d_pending, d_popc, d_prefix, d_block_sums;
@@ -312,7 +314,7 @@ int rebuild_index(kgx_ctx* c) {
 }
 
 void free_table_state(kgx_ctx* c) {
-  DBuf* all[] = {&c->d_node_tab, &c->d_tab, &c->d_pk_slot0, &c->d_pk_stride, &c->d_grank, &c->d_node_slot_base,
+  DBuf* all[] = {&c->d_node_a_base, &c->d_node_tab, &c->d_tab, &c->d_pk_slot0, &c->d_pk_stride, &c->d_grank, &c->d_node_slot_base,
                  &c->d_A_blob, &c->d_B_blob, &c->d_G_blob, &c->d_A_off, &c->d_B_off, &c->d_G_off, &c->d_runs,
                  &c->d_bm, &c->d_pending, &c->d_popc, &c->d_prefix, &c->d_ser_slot, &c->d_ser_a, &c->d_ser_gidx,
                  &c->d_ser_len, &c->d_lbl_off, &c->d_lbl_blob, &c->d_node_ser_off, &c->d_node_live, &c->d_gpu_total,
@@ -350,6 +352,17 @@ int upload_plan(kgx_ctx* c) {
   KGX_TRY(upload(c, c->d_pk_slot0, p.pk_slot0.data(), p.pk_slot0.size()));
   KGX_TRY(upload(c, c->d_pk_stride, p.pk_stride.data(), p.pk_stride.size()));
   KGX_TRY(upload(c, c->d_grank, p.grank.data(), p.grank.size()));
+  KGX_TRY(upload(c, c->d_node_a_base, p.node_a_base.data(), p.node_a_base.size()));
+  {  // node-grouped join: stage a node's table slice (+ its podkey slot tables) in shared memory when it fits
+    const uint64_t budget = 100 * 1024;  // two CTAs per SM
+    const uint64_t need = uint64_t(p.max_node_cells) * sizeof(Entry) + uint64_t(p.max_node_pks) * 8;
+    if (need <= budget) { c->ingest_cells = p.max_node_cells; c->ingest_pks = p.max_node_pks; }
+    else { c->ingest_cells = 0; c->ingest_pks = 0; }  // too large: probe in global memory, still node by node
+    c->ingest_smem = uint32_t(uint64_t(c->ingest_cells) * sizeof(Entry) + uint64_t(c->ingest_pks) * 8 + 16);
+    const void* fns[] = {(const void*)&k_ingest_nodes<true, 0>, (const void*)&k_ingest_nodes<true, 1>,
+                         (const void*)&k_ingest_nodes<false, 0>, (const void*)&k_ingest_nodes<false, 1>};
+    for (const void* f : fns) KGX_CUDA(c, cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->ingest_smem)));
+  }
   KGX_TRY(upload(c, c->d_node_slot_base, p.node_slot_base.data(), p.node_slot_base.size()));
   KGX_TRY(upload(c, c->d_A_blob, p.A_blob.data(), p.A_blob.size()));
   KGX_TRY(upload(c, c->d_B_blob, p.B_blob.data(), p.B_blob.size()));
@@ -430,10 +443,26 @@ int ingest_device_locked(kgx_ctx* c, const kgx_cols* s) {
   DevCols dc{s->pid, s->gpu, s->node, s->sm_util, s->mem_util, reinterpret_cast<const unsigned long long*>(s->used),
              reinterpret_cast<const unsigned long long*>(s->ts_us), reinterpret_cast<const unsigned long long*>(s->node_off), s->n};
   const int grid = int(std::min<uint64_t>(uint64_t(c->sm_count) * 8, std::max<uint64_t>(1, cdiv(s->n, 256))));
+  // rows grouped by node: one CTA per node, table slice staged in shared memory
+  const bool grouped = s->node_off != nullptr && !getenv("KGX_INGEST_V1");
+  const DevNodeMeta nm{ptr<uint32_t>(c->d_node_a_base), c->ingest_cells, c->ingest_pks};
+  const int ngrid = int(std::min<uint32_t>(p.n_nodes, uint32_t(c->sm_count) * 2));
+  auto launch_ingest = [&](int pass) {
+    if (grouped) {
+      if (x && pass == 0) k_ingest_nodes<true, 0><<<ngrid, kIngestThreads, c->ingest_smem, c->stream>>>(t, nm, ix, acc_view(c), dc, c->seq, ctr);
+      else if (x) k_ingest_nodes<true, 1><<<ngrid, kIngestThreads, c->ingest_smem, c->stream>>>(t, nm, ix, acc_view(c), dc, c->seq, ctr);
+      else if (pass == 0) k_ingest_nodes<false, 0><<<ngrid, kIngestThreads, c->ingest_smem, c->stream>>>(t, nm, ix, acc_view(c), dc, c->seq, ctr);
+      else k_ingest_nodes<false, 1><<<ngrid, kIngestThreads, c->ingest_smem, c->stream>>>(t, nm, ix, acc_view(c), dc, c->seq, ctr);
+    } else {
+      if (x && pass == 0) k_ingest<true, 0><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
+      else if (x) k_ingest<true, 1><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
+      else if (pass == 0) k_ingest<false, 0><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
+      else k_ingest<false, 1><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
+    }
+  };
   if (s->n) {
     Timed tm(c, KGX_K_INGEST);
-    if (x) k_ingest<true, 0><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
-    else k_ingest<false, 0><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
+    launch_ingest(0);
     tm.launches(1);
     KGX_TRY(launch_check(c, "k_ingest"));
   }
@@ -445,8 +474,7 @@ int ingest_device_locked(kgx_ctx* c, const kgx_cols* s) {
     KGX_TRY(rebuild_index(c));
     {
       Timed tm(c, KGX_K_INGEST);
-      if (x) k_ingest<true, 1><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
-      else k_ingest<false, 1><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
+      launch_ingest(1);
       tm.launches(1);
       KGX_TRY(launch_check(c, "k_ingest churn pass"));
     }

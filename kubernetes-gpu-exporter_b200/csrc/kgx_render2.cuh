@@ -1,23 +1,31 @@
 // kgx_render2.cuh — exposition writer, second generation (sm_100a).
 //
 // Same contract as k_render (byte-identical output; replaces what main.go:69-71
-// serves through Registry.Gather + expfmt), rebuilt around how the bytes move:
+// serves through Registry.Gather + expfmt), rebuilt around how the bytes move
+// and around what has to wait for what:
 //
 //   * the label text of a tile is ONE contiguous byte range of the series label
 //     blob: a single TMA bulk copy (cp.async.bulk global->shared, completion on
-//     an mbarrier) stages it while the threads format their values;
+//     an mbarrier) stages it.  Warp 0 issues it for the NEXT tile — together
+//     with that tile's ticket and descriptor — while the CTA is still flushing
+//     the current one, so neither the ticket, nor the descriptor, nor the
+//     labels are waited for;
 //   * each thread owns one line and formats its value once, straight into a
 //     shared-memory slot (" <value>\n");
-//   * line lengths -> CTA scan -> inter-tile decoupled look-back give every
-//     line its exact byte offset;
-//   * each thread then streams its line into the shared output buffer as
-//     16-byte chunks ALIGNED TO THE GLOBAL ADDRESS: a chunk belongs to the line
-//     that holds its first byte, so every store is a full STS.128 and no two
-//     threads touch the same chunk.  Sources (metric name, staged labels, value
-//     slot, the next line's name prefix) are read with word loads + funnel
-//     shifts; only the 2-3 chunks that straddle two sources need a byte merge;
-//   * the finished tile leaves with one TMA bulk store (shared->global); the
-//     few bytes before/after the 16-byte-aligned body go out as byte stores.
+//   * line lengths -> CTA scan; the tile's size is published to the look-back
+//     chain at once, so successors never wait for more than this;
+//   * each thread streams its line into the shared output buffer as aligned
+//     16-byte chunks: a chunk belongs to the line that holds its first byte, so
+//     every store is a full STS.128 and no two threads touch the same chunk.
+//     The four sources of a line (metric name, staged labels, value slot, the
+//     next line's name prefix) are appended one after the other, all lanes in
+//     lock-step; word loads + funnel shifts realign, a mask table merges the
+//     one chunk that straddles two sources;
+//   * only then does warp 0 resolve the tile's global byte offset (decoupled
+//     look-back, 32 predecessors per step): by now they have all published;
+//   * the tile leaves through the LSU: every lane re-aligns 16 bytes from the
+//     tile buffer to the global address (2 x LDS.128 + funnel shift) and issues
+//     one streaming STG.128; the <16 bytes at either end go as byte stores.
 #pragma once
 #include "kgx_kernels.cuh"
 
@@ -25,8 +33,8 @@ namespace kgx {
 
 struct RenderLayout {  // byte offsets inside dynamic shared memory (all 16-aligned)
   uint32_t names;      // kMaxFamilies x 96: [16 pad][name (<=64)][16 pad]
-  uint32_t slots;      // tile_lines x 28: " <value>\n"
-  uint32_t stage;      // staged label text (+32 slack either side)
+  uint32_t slots;      // THREADS x 28: " <value>\n"
+  uint32_t stage;      // staged label text (+32 slack before, +128+48 after)
   uint32_t out;        // the tile's output text
   uint32_t total;
 };
@@ -36,6 +44,11 @@ constexpr uint32_t kNameStride = 96;
 __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
   uint32_t v;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
   return v;
 }
 __device__ __forceinline__ void sts128(uint32_t addr, uint4 v) {
@@ -51,8 +64,7 @@ __device__ __forceinline__ uint4 gather16(uint32_t a) {
 // bytes [0,e) from lo, bytes [e,16) from hi (0 < e < 16); mask_sm: shared table of
 // 16 byte masks, entry e = the first e bytes set
 __device__ __forceinline__ uint4 merge16(uint4 lo, uint4 hi, uint32_t e, uint32_t mask_sm) {
-  uint4 m;
-  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(m.x), "=r"(m.y), "=r"(m.z), "=r"(m.w) : "r"(mask_sm + 16u * e));
+  const uint4 m = lds128(mask_sm + 16u * e);
   return make_uint4((lo.x & m.x) | (hi.x & ~m.x), (lo.y & m.y) | (hi.y & ~m.y), (lo.z & m.z) | (hi.z & ~m.z),
                     (lo.w & m.w) | (hi.w & ~m.w));
 }
@@ -78,19 +90,17 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
                "l"(src), "r"(bytes), "r"(bar)
                : "memory");
 }
-// TMA bulk copy shared -> global
-__device__ __forceinline__ void bulk_s2g(void* dst, uint32_t src, uint32_t bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
-}
 
 template <int THREADS>
 __global__ void __launch_bounds__(THREADS) k_render2(DevRender R, RenderLayout lay, DevAcc acc, unsigned long long* counters) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ unsigned long long s_scan[THREADS / 32];
-  __shared__ uint32_t s_tile;
   __shared__ unsigned long long s_base;
   __shared__ __align__(8) unsigned long long s_bar;
   __shared__ __align__(16) uint32_t s_mask[16][4];
+  __shared__ uint32_t s_next;          // ticket of the tile to process next
+  __shared__ Tile s_desc;              // its descriptor
+  __shared__ unsigned long long s_g0;  // start of its staged label range in the blob (128-aligned)
   const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const uint32_t sm0 = uint32_t(__cvta_generic_to_shared(smem));
   const uint32_t bar = uint32_t(__cvta_generic_to_shared(&s_bar));
@@ -110,30 +120,18 @@ __global__ void __launch_bounds__(THREADS) k_render2(DevRender R, RenderLayout l
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  uint32_t parity = 0;
-  for (;;) {
-    if (tid == 0) s_tile = uint32_t(atomicAdd(&counters[C_TICKET], 1ull));
-    __syncthreads();
-    const uint32_t t = s_tile;
-    if (t >= R.n_tiles) {
-      if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // my bulk stores have fully landed
-      return;
-    }
-    const Tile tile = R.tiles[t];
-    const FamMeta& fm = R.fam[tile.family];
-    const uint32_t name_len = fm.name_len;
-    // ---- stage the tile's label text: one bulk copy of an aligned superset
-    const unsigned long long L0 = R.lbl_off[tile.first];
-    const unsigned long long g0 = L0 & ~127ull;  // whole 128-byte lines: the copy engine's natural unit
-    if (R.flags & 2) {  // staged by every thread with 16-byte cp.async (LDGSTS) instead of the TMA engine
-      const unsigned long long L1 = R.lbl_off[tile.first + tile.count];
-      const uint32_t chunks = uint32_t(((L1 + 15ull) & ~15ull) - g0) >> 4;
-      const uint8_t* src = R.lbl_blob + g0;
-      for (uint32_t i = tid; i < chunks; i += THREADS)
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sm0 + lay.stage + 32 + 16 * i), "l"(src + 16 * size_t(i)) : "memory");
-      asm volatile("cp.async.commit_group;" ::: "memory");
-    } else if (tid == 0) {
-      const unsigned long long L1 = R.lbl_off[tile.first + tile.count];
+
+  // Warp 0: take the next ticket (tiles are handed out in output order, so the
+  // look-back never waits on a tile that has not started), read its descriptor
+  // and start the bulk copy of its label text.
+  auto fetch_next = [&]() {
+    uint32_t nt = 0;
+    if (lane == 0) nt = uint32_t(atomicAdd(&counters[C_TICKET], 1ull));
+    nt = __shfl_sync(0xffffffffu, nt, 0);
+    if (nt < R.n_tiles && lane == 0) {
+      const Tile d = R.tiles[nt];
+      const unsigned long long L0 = R.lbl_off[d.first], L1 = R.lbl_off[d.first + d.count];
+      const unsigned long long g0 = L0 & ~127ull;  // whole 128-byte lines
       const uint32_t bytes = uint32_t(((L1 + 15ull) & ~15ull) - g0);
       if (bytes) {
         mbar_expect_tx(bar, bytes);
@@ -141,7 +139,23 @@ __global__ void __launch_bounds__(THREADS) k_render2(DevRender R, RenderLayout l
       } else {
         asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
       }
+      s_desc = d;
+      s_g0 = g0;
     }
+    if (lane == 0) s_next = nt;
+  };
+  if (wid == 0) fetch_next();
+  __syncthreads();
+
+  uint32_t parity = 0;
+  const uint32_t outb = sm0 + lay.out;  // byte p of the tile lives at outb + p
+  for (;;) {
+    const uint32_t t = s_next;
+    if (t >= R.n_tiles) return;
+    const Tile tile = s_desc;
+    const unsigned long long g0 = s_g0;
+    const FamMeta& fm = R.fam[tile.family];
+    const uint32_t name_len = fm.name_len;
     // ---- pass 1: value text and exact length of my line
     const uint32_t slot = sm0 + lay.slots + tid * kSlotBytes;
     uint32_t len = 0, lbl_len = 0, vlen = 0, lbl_src = 0;
@@ -166,21 +180,50 @@ __global__ void __launch_bounds__(THREADS) k_render2(DevRender R, RenderLayout l
     unsigned long long inc = mine;
     for (int o = 1; o < 32; o <<= 1) { unsigned long long u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
     if (lane == 31) s_scan[wid] = inc;
-    __syncthreads();
+    __syncthreads();  // (1) also: everyone has read s_next / s_desc / s_g0
     unsigned long long woff = 0, all = 0;
     for (int k = 0; k < THREADS / 32; ++k) { if (k < int(wid)) woff += s_scan[k]; all += s_scan[k]; }
     const unsigned long long exc = woff + inc - mine;
     const uint32_t off = hdr + uint32_t(exc);
     const uint32_t total = hdr + uint32_t(all);
     const bool first_live = live && uint32_t(exc >> 32) == 0;
-    const bool last_live = live && uint32_t(exc >> 32) + 1 == uint32_t(all >> 32);
-    // ---- inter-tile offset: decoupled look-back over the tile chain
-    // Warp 0 inspects 32 predecessors per step: everything after the nearest tile
-    // that already knows its inclusive prefix contributes its own size.
+    // the tile's size is all a successor needs from us until it resolves its own offset
+    if (tid == 0 && t > 0) atomicExch(&R.tile_state[t], kStAgg | total);
+    mbar_wait(bar, parity);  // staged labels have landed (issued a whole tile ago)
+    parity ^= 1;
+    // ---- pass 2: stream my line into the tile buffer as aligned 16-byte chunks
+    if (live) {
+      const uint32_t g = outb + off;                                            // first byte of my line
+      const uint32_t b0 = g + name_len, b1 = b0 + lbl_len, b2 = b1 + vlen + 2;  // source boundaries; b2 = line end
+      const uint32_t start = first_live ? (g & ~15u) : ((g + 15u) & ~15u);
+      const uint32_t stop = (b2 + 15u) & ~15u;  // my chunks: [start, stop)
+      const uint32_t name_sm = sm0 + lay.names + tile.family * kNameStride + 16;
+      const uint32_t d0 = name_sm - g, d1 = lbl_src - b0, d2 = slot - b1, d3 = name_sm - b2;  // source = position + delta
+      // `a4` holds the chunk at p, of which the first `e` bytes are already final.
+      uint32_t p = start, e = 0;
+      uint4 a4 = make_uint4(0, 0, 0, 0);
+      auto append = [&](uint32_t d, uint32_t b) {  // source = position + d, up to position b (exclusive)
+        const uint4 nw = gather16(p + d);
+        a4 = e ? merge16(a4, nw, e, mask_sm) : nw;
+        if (b >= p + 16) {
+          sts128(p, a4);
+          p += 16;
+          while (p + 16 <= b) { sts128(p, gather16(p + d)); p += 16; }
+          a4 = gather16(p + d);
+        }
+        e = b - p;
+      };
+      append(d0, b0);    // metric name (the first line of a tile also owns the chunk its line starts in)
+      append(d1, b1);    // labels
+      append(d2, b2);    // " <value>\n"
+      append(d3, stop);  // the head of the next line's name completes my last chunk
+    }
+    __syncthreads();  // (2) tile text complete; label stage and value slots are free
+    if (hdr) for (uint32_t i = tid; i < hdr; i += THREADS) smem[lay.out + i] = fm.header[i];
+    // ---- global byte offset of the tile: decoupled look-back, 32 predecessors per step
     if (wid == 0) {
       unsigned long long base = 0;
       if (t > 0) {
-        if (lane == 0) atomicExch(&R.tile_state[t], kStAgg | total);
         long long p = (long long)t - 1 - lane;  // lane 0 looks at the direct predecessor
         for (;;) {
           unsigned long long s = kStPrefix;     // before tile 0: an inclusive prefix of zero
@@ -199,75 +242,40 @@ __global__ void __launch_bounds__(THREADS) k_render2(DevRender R, RenderLayout l
       if (lane == 0) {
         atomicExch(&R.tile_state[t], kStPrefix | (base + total));
         s_base = base;
-        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // previous tile's bulk store has read the output buffer
         if (tile.flags & 2) R.node_body_off[tile.node] = base;
         if (t == R.n_tiles - 1) counters[C_TOTAL_LEN] = base + total;
       }
     }
-    if (R.flags & 2) asm volatile("cp.async.wait_group 0;" ::: "memory");  // my share of the label copy has landed
-    __syncthreads();
+    __syncthreads();  // (3)
     const unsigned long long base = s_base;
-    const uint32_t sh = uint32_t(base & 15);   // shared offset == global address (mod 16)
-    const uint32_t outb = sm0 + lay.out;       // byte p of the tile lives at outb + sh + p
-    if (!(R.flags & 2)) { mbar_wait(bar, parity); parity ^= 1; }  // staged labels have landed
-    // ---- pass 2: stream my line into the output buffer as aligned 16-byte chunks
-    if (live) {
-      const uint32_t g = outb + sh + off;                    // first byte of my line
-      const uint32_t b0 = g + name_len, b1 = b0 + lbl_len, b2 = b1 + vlen + 2;  // source boundaries; b2 = line end
-      const uint32_t start = first_live ? (g & ~15u) : ((g + 15u) & ~15u);
-      const uint32_t stop = (b2 + 15u) & ~15u;               // my chunks: [start, stop)
-      const uint32_t name_sm = sm0 + lay.names + tile.family * kNameStride + 16;
-      const uint32_t d0 = name_sm - g, d1 = lbl_src - b0, d2 = slot - b1, d3 = name_sm - b2;  // source = position + delta
-      (void)last_live;  // after the last line the chunk tail is slack: never copied out
-      // The four sources are appended one after the other, so that all lanes of
-      // a warp are in the same source at the same time (no per-chunk branching
-      // on where the boundaries fall): `acc` holds the chunk at p, of which the
-      // first `e` bytes are already final.
-      uint32_t p = start, e = 0;
-      uint4 a4 = make_uint4(0, 0, 0, 0);
-      auto append = [&](uint32_t d, uint32_t b) {  // source = position + d, up to position b (exclusive)
-        const uint4 nw = gather16(p + d);
-        a4 = e ? merge16(a4, nw, e, mask_sm) : nw;
-        if (b >= p + 16) {
-          sts128(p, a4);
-          p += 16;
-          while (p + 16 <= b) { sts128(p, gather16(p + d)); p += 16; }
-          a4 = gather16(p + d);
-        }
-        e = b - p;
-      };
-      append(d0, b0);
-      append(d1, b1);
-      append(d2, b2);
-      append(d3, stop);
-    }
-    if (hdr) {  // the header goes in after the lines: the first line's leading chunk overlaps its tail
-      __syncthreads();
-      for (uint32_t i = tid; i < hdr; i += THREADS) smem[lay.out + sh + i] = fm.header[i];
-    }
-    if (R.flags & 1) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the bulk store
-    __syncthreads();
-    // ---- the tile leaves: byte head, bulk body, byte tail
+    if (wid == 0) fetch_next();  // next ticket, descriptor and label copy overlap the flush
+    // ---- the tile leaves: re-align to the global address, 16 bytes per lane
     uint8_t* gout = R.out + base;
-    const uint32_t head = min(total, (16u - sh) & 15u);
-    const uint32_t body = (total - head) & ~15u;
-    if (R.flags & 1) {  // body through the TMA engine (one bulk store)
-      if (tid == 0 && body) {
-        bulk_s2g(gout + head, outb + sh + head, body);
-        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-      }
-    } else {            // body through the LSU: 16 bytes per lane, fully coalesced
-      const uint4* sb = reinterpret_cast<const uint4*>(smem + lay.out + sh + head);
+    const uint32_t head = min(total, uint32_t((16u - uint32_t(base & 15)) & 15u));
+    const uint32_t nbody = (total - head) >> 4;
+    const uint32_t tailb = total - head - 16u * nbody;
+    {
+      const uint32_t src0 = outb + head;  // shared address of the first body byte: same shift for the whole tile
+      const uint32_t q = (src0 >> 2) & 3u, r = (src0 & 3u) * 8u;
       uint4* gb = reinterpret_cast<uint4*>(gout + head);
-      for (uint32_t i = tid; i < body / 16; i += THREADS) __stcs(gb + i, sb[i]);
+      for (uint32_t i = tid; i < nbody; i += THREADS) {
+        const uint32_t a = (src0 & ~15u) + 16u * i;
+        const uint4 x = lds128(a), y = lds128(a + 16);
+        uint32_t w0, w1, w2, w3, w4;  // the five words that cover the 16 wanted bytes
+        if (q == 0) { w0 = x.x; w1 = x.y; w2 = x.z; w3 = x.w; w4 = y.x; }
+        else if (q == 1) { w0 = x.y; w1 = x.z; w2 = x.w; w3 = y.x; w4 = y.y; }
+        else if (q == 2) { w0 = x.z; w1 = x.w; w2 = y.x; w3 = y.y; w4 = y.z; }
+        else { w0 = x.w; w1 = y.x; w2 = y.y; w3 = y.z; w4 = y.w; }
+        __stcs(gb + i, make_uint4(__funnelshift_r(w0, w1, r), __funnelshift_r(w1, w2, r), __funnelshift_r(w2, w3, r),
+                                  __funnelshift_r(w3, w4, r)));
+      }
     }
-    if (tid < head) gout[tid] = smem[lay.out + sh + tid];
-    if (tid >= 16 && tid < 16 + (total - head - body)) {
-      const uint32_t i = head + body + tid - 16;
-      gout[i] = smem[lay.out + sh + i];
+    if (tid < head) gout[tid] = smem[lay.out + tid];
+    if (tid >= 16 && tid < 16 + tailb) {
+      const uint32_t i = head + 16u * nbody + tid - 16;
+      gout[i] = smem[lay.out + i];
     }
-    // no barrier here: the next tile's first barriers order everything, and the bulk
-    // store's reads of the output buffer are awaited right before it is rewritten
+    __syncthreads();  // (4) tile buffer free; s_next / s_desc / s_g0 of the next tile visible
   }
 }
 

@@ -166,6 +166,7 @@ int build_plan(int mode, const kgx_table* t, const std::vector<Carried>& carried
 
   if (x) {
     p.grank.assign(size_t(NN) * G, 0);
+    p.node_a_base.assign(size_t(NN) + 1, 0);
     for (size_t g = 0; g < size_t(NN) * G; ++g) {
       std::string_view u = sv(t->gpu_uuid_blob, t->gpu_uuid_off, g);
       if (!valid_utf8(u)) return fail(KGX_E_INVAL, "table: gpu uuid is not valid UTF-8");
@@ -205,6 +206,8 @@ int build_plan(int mode, const kgx_table* t, const std::vector<Carried>& carried
         if (gsv(gord[r - 1]) == gsv(gord[r])) return fail(KGX_E_INVAL, "table: duplicate gpu uuid on one node");
       for (uint32_t r = 0; r < G; ++r) p.grank[size_t(n) * G + gord[r]] = r;
       const uint32_t a_base = uint32_t(p.n_a);
+      p.node_a_base[n] = a_base;
+      p.max_node_pks = std::max<uint32_t>(p.max_node_pks, uint32_t(pks.size()));
       std::unordered_map<uint32_t, uint32_t> a_of_pk;
       a_of_pk.reserve(pks.size() * 2);
       size_t i = 0;
@@ -309,12 +312,14 @@ int build_plan(int mode, const kgx_table* t, const std::vector<Carried>& carried
       std::sort(cells.begin(), cells.end());
     }
     p.node_tab[n] = NodeTab{uint32_t(tab_total), table_capacity(cells.size())};
+    p.max_node_cells = std::max(p.max_node_cells, p.node_tab[n].cap);
     tab_total += p.node_tab[n].cap;
     if (tab_total >= 0xfffffff0ull) return fail(KGX_E_LIMIT, "table: hash table beyond 2^32 cells");
     p.n_table_entries += cells.size();
     node_cells[n] = cells;
   }
   p.node_slot_base[NN] = uint32_t(slot_total);
+  if (x) p.node_a_base[NN] = uint32_t(p.n_a);
   p.n_slots = slot_total;
   if (!x) p.B_off.assign(size_t(p.n_a) + 1, 0);
   // pass 2: the open-addressing table

@@ -47,6 +47,8 @@ struct Plan {
   std::vector<Entry> tab;
   std::vector<uint32_t> pk_slot0, pk_stride;  // X: per sorted podkey
   std::vector<uint32_t> grank;                // X: [n_nodes*G] order of the gpu label value in its node
+  std::vector<uint32_t> node_a_base;          // X: [n_nodes+1] first sorted-podkey index of each node
+  uint32_t max_node_cells = 0, max_node_pks = 0;  // largest per-node table slice / podkey count
   // label pieces: text of slot s = A[a] + GL[gidx] + B[a]
   std::string A_blob, B_blob, G_blob;
   std::vector<uint64_t> A_off, B_off, G_off;
