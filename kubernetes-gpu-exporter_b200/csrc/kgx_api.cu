@@ -42,7 +42,7 @@ struct kgx_ctx {
   Plan plan;
   // table
   DBuf d_node_tab, d_tab, d_pk_slot0, d_pk_stride, d_grank, d_node_slot_base, d_node_a_base;
-  uint32_t ingest_smem = 0, ingest_cells = 0, ingest_pks = 0;  // staging buffer of the node-grouped join
+  uint32_t ingest_smem = 0, ingest_cells = 0, ingest_pks = 0, ingest_words = 0;  // staging buffer of the node-grouped join
   DBuf d_A_blob, d_B_blob, d_G_blob, d_A_off, d_B_off, d_G_off, d_runs;
   // index
   DBuf d_bm, d_pending, d_popc, d_prefix, d_block_sums;
@@ -355,10 +355,13 @@ int upload_plan(kgx_ctx* c) {
   KGX_TRY(upload(c, c->d_node_a_base, p.node_a_base.data(), p.node_a_base.size()));
   {  // node-grouped join: stage a node's table slice (+ its podkey slot tables) in shared memory when it fits
     const uint64_t budget = 100 * 1024;  // two CTAs per SM
-    const uint64_t need = uint64_t(p.max_node_cells) * sizeof(Entry) + uint64_t(p.max_node_pks) * 8;
-    if (need <= budget) { c->ingest_cells = p.max_node_cells; c->ingest_pks = p.max_node_pks; }
-    else { c->ingest_cells = 0; c->ingest_pks = 0; }  // too large: probe in global memory, still node by node
-    c->ingest_smem = uint32_t(uint64_t(c->ingest_cells) * sizeof(Entry) + uint64_t(c->ingest_pks) * 8 + 16);
+    uint32_t max_words = 0;  // series-index words one node spans
+    for (uint32_t n = 0; n < p.n_nodes; ++n)
+      max_words = std::max(max_words, ((p.node_slot_base[n + 1] + 31) >> 5) - (p.node_slot_base[n] >> 5));
+    const uint64_t need = uint64_t(p.max_node_cells) * sizeof(Entry) + uint64_t(p.max_node_pks) * 8 + uint64_t(max_words) * 8;
+    if (need <= budget) { c->ingest_cells = p.max_node_cells; c->ingest_pks = p.max_node_pks; c->ingest_words = max_words; }
+    else { c->ingest_cells = 0; c->ingest_pks = 0; c->ingest_words = 0; }  // too large: probe in global memory, still node by node
+    c->ingest_smem = uint32_t(uint64_t(c->ingest_cells) * sizeof(Entry) + uint64_t(c->ingest_pks) * 8 + uint64_t(c->ingest_words) * 8 + 16);
     const void* fns[] = {(const void*)&k_ingest_nodes<true, 0>, (const void*)&k_ingest_nodes<true, 1>,
                          (const void*)&k_ingest_nodes<false, 0>, (const void*)&k_ingest_nodes<false, 1>};
     for (const void* f : fns) KGX_CUDA(c, cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->ingest_smem)));
@@ -445,7 +448,7 @@ int ingest_device_locked(kgx_ctx* c, const kgx_cols* s) {
   const int grid = int(std::min<uint64_t>(uint64_t(c->sm_count) * 8, std::max<uint64_t>(1, cdiv(s->n, 256))));
   // rows grouped by node: one CTA per node, table slice staged in shared memory
   const bool grouped = s->node_off != nullptr && !getenv("KGX_INGEST_V1");
-  const DevNodeMeta nm{ptr<uint32_t>(c->d_node_a_base), c->ingest_cells, c->ingest_pks};
+  const DevNodeMeta nm{ptr<uint32_t>(c->d_node_a_base), c->ingest_cells, c->ingest_pks, ptr<uint32_t>(c->d_node_slot_base), c->ingest_words};
   const int ngrid = int(std::min<uint32_t>(p.n_nodes, uint32_t(c->sm_count) * 2));
   auto launch_ingest = [&](int pass) {
     if (grouped) {

@@ -24,7 +24,10 @@ struct DevNodeMeta {
   const uint32_t* node_a_base;  // X: [n_nodes+1] first sorted-podkey index of each node
   uint32_t smem_cells;          // table cells that fit the staging buffer
   uint32_t smem_pks;            // podkeys that fit the staging buffer
+  const uint32_t* node_slot_base;  // [n_nodes+1] first slot of each node
+  uint32_t smem_words;          // series-index words (32 slots each) that fit the staging buffer
 };
+constexpr uint32_t kMaxStagedGpus = 64;
 
 template <bool XMODE, int PASS>
 __global__ void __launch_bounds__(kIngestThreads) k_ingest_nodes(DevTable t, DevNodeMeta nm, DevIndex ix, DevAcc acc, DevCols c,
@@ -36,6 +39,8 @@ __global__ void __launch_bounds__(kIngestThreads) k_ingest_nodes(DevTable t, Dev
   Entry* s_tab = reinterpret_cast<Entry*>(smem);
   uint32_t* s_slot0 = reinterpret_cast<uint32_t*>(smem + size_t(nm.smem_cells) * sizeof(Entry));
   uint32_t* s_stride = s_slot0 + nm.smem_pks;
+  uint2* s_bm = reinterpret_cast<uint2*>(s_stride + nm.smem_pks);  // the node's slice of the series index
+  __shared__ uint32_t s_grank[kMaxStagedGpus];
   if (tid == 0) {
     mbar_init(bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -50,7 +55,8 @@ __global__ void __launch_bounds__(kIngestThreads) k_ingest_nodes(DevTable t, Dev
     const NodeTab nt = t.node_tab[node];
     uint32_t a0 = 0, K = 0;
     if (XMODE) { a0 = nm.node_a_base[node]; K = nm.node_a_base[node + 1] - a0; }
-    const bool staged = nt.cap <= nm.smem_cells && K <= nm.smem_pks;
+    const uint32_t w0 = nm.node_slot_base[node] >> 5, w1 = (nm.node_slot_base[node + 1] + 31) >> 5;
+    const bool staged = nt.cap <= nm.smem_cells && K <= nm.smem_pks && (w1 - w0) <= nm.smem_words && t.G <= kMaxStagedGpus;
     if (staged) {
       if (tid == 0) {  // the node's table slice: one contiguous, 64-byte aligned range
         mbar_expect_tx(bar, nt.cap * uint32_t(sizeof(Entry)));
@@ -58,10 +64,13 @@ __global__ void __launch_bounds__(kIngestThreads) k_ingest_nodes(DevTable t, Dev
       }
       if (XMODE)
         for (uint32_t i = tid; i < K; i += kIngestThreads) { s_slot0[i] = t.pk_slot0[a0 + i]; s_stride[i] = t.pk_stride[a0 + i]; }
+      for (uint32_t i = tid; i < w1 - w0; i += kIngestThreads) s_bm[i] = ix.bm[w0 + i];
+      if (XMODE && tid < t.G) s_grank[tid] = t.grank[node * t.G + tid];
       mbar_wait(bar, parity);
       parity ^= 1;
       __syncthreads();
     }
+    bool marked_live = false;
     for (unsigned long long i = lo + tid; i < hi; i += kIngestThreads) {
       const uint32_t gpu = c.gpu[i];
       if (gpu >= t.G) { ++dropped; continue; }
@@ -76,13 +85,13 @@ __global__ void __launch_bounds__(kIngestThreads) k_ingest_nodes(DevTable t, Dev
           const uint32_t target = e.val & ~kMore;
           uint32_t slot;
           if (XMODE) {
-            const uint32_t gr = t.grank[node * t.G + gpu];
+            const uint32_t gr = staged ? s_grank[gpu] : t.grank[node * t.G + gpu];
             slot = staged ? s_slot0[target - a0] + gr * s_stride[target - a0] : t.pk_slot0[target] + gr * t.pk_stride[target];
           } else {
             slot = target;
           }
           const uint32_t w = slot >> 5, bit = 1u << (slot & 31);
-          const uint2 b = ix.bm[w];
+          const uint2 b = staged ? s_bm[w - w0] : ix.bm[w];
           bool fold;
           if (PASS == 0) {
             fold = (b.x & bit) != 0;
@@ -94,7 +103,8 @@ __global__ void __launch_bounds__(kIngestThreads) k_ingest_nodes(DevTable t, Dev
             const uint32_t r = b.y + __popc(b.x & (bit - 1));
             if (XMODE) {
               const unsigned long long used = c.used[i];
-              if (atomicAdd(&acc.count[r], 1ull) == 0) atomicAdd(&acc.node_live[node], 1u);
+              atomicAdd(&acc.count[r], 1ull);
+              if (!marked_live) { acc.node_live[node] = 1; marked_live = true; }  // only "non-zero" matters: plain store
               atomicAdd(&acc.sum_used[r], used);
               atomicMax(&acc.max_used[r], used);
               atomicMax(&acc.last_ts[r], c.ts_us[i]);
