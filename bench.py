@@ -167,6 +167,8 @@ def main():
     ap.add_argument("--ref-nodes", type=int, default=100, help="nodes in the CPU sample")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--gather", action="store_true",
+                    help="N>1: also time the ordered concatenation of all bodies on rank 0 (NCCL send/recv over NVLink)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "kgx" else args.warmup
     if args.impl == "reference":
@@ -295,6 +297,28 @@ def main():
         e2e = {"value": total_samples / (float(tm.item()) * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(n_out), "ms_per_step": float(tm.item()), "host_memory": "pinned (kgx_host_alloc)"}
 
+    # ---- optional: ordered concatenation of the per-GPU bodies on rank 0 ------------------
+    gather = None
+    if args.gather and world > 1:
+        from kgx_b200 import fleetshard
+        g.render_device()
+        ptr_, n_ = g.body_device()
+        local = torch.as_tensor(fleetshard.DeviceBytes(ptr_, n_), device=dev)
+        _, offs = fleetshard.gather_layout(n_, device=dev)
+        root_out = torch.empty(int(offs[-1]), dtype=torch.uint8, device=dev) if rank == 0 else None
+        for _ in range(2):
+            fleetshard.gather_bodies(local, dst=0, out=root_out)
+        barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        for _ in range(5):
+            fleetshard.gather_bodies(local, dst=0, out=root_out)
+        g1.record()
+        barrier()
+        gms = fleetshard.max_over_ranks(g0.elapsed_time(g1) / 5, device=dev)
+        gather = {"ms": gms, "bytes_on_root": int(offs[-1]), "inbound_gbs": (int(offs[-1]) - n_) / (gms * 1e-3) / 1e9 if rank == 0 else None,
+                  "how": "lengths all-gather + NCCL send/recv into rank 0's buffer, bodies stay in node order"}
+
     # ---- CPU baseline on this box's host cores (rank 0, N=1 only) --------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -307,7 +331,7 @@ def main():
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_max, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64/f64",
                 "data": "synthetic", "config": workload_config(args.nodes), "clocks": clk, "e2e": e2e,
-                "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+                "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "gather": gather,
                 "series_per_gpu": int(series), "rendered_bytes_per_gpu": int(body_len),
                 "kernel_ms": {k: v[0] / max(1, args.steps) for k, v in prof.items()}}
         print(json.dumps(line), flush=True)
