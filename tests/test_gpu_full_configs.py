@@ -1,0 +1,96 @@
+"""Parity at BASELINE.json's full sizes.  Where the oracle finishes in seconds
+(rack replay, 1 M samples) the whole body is compared byte for byte; for the
+10 M-sample fleet the oracle renders a sample of nodes (their bodies are
+independent: one /metrics body per node) and size-independent properties cover
+the rest; the 60-scrape window is folded on both sides and compared whole."""
+import os
+
+import numpy as np
+import pytest
+
+from kgx_b200 import build, kgx
+from kgx_b200.abi import MODE_R_INTENDED, MODE_X
+from kgx_b200.fleet import Fleet
+
+pytestmark = pytest.mark.gpu
+THREADS = min(16, os.cpu_count() or 1)
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _built():
+    build.build()
+
+
+@pytest.mark.parametrize("mode", [MODE_R_INTENDED, MODE_X])
+def test_rack_replay_1m_samples_bit_exact(kgo, mode):
+    """configs[2]: 128 nodes, 128k pods, 1M process samples."""
+    f = Fleet.config(3)
+    t, s = f.table(mode), f.scrape(0)
+    g, o = kgx.Kgx(mode), kgo.Oracle(mode, kgo.JOIN_HASH, THREADS)
+    g.set_table(t); o.set_table(t)
+    g.ingest(s); o.ingest(s)
+    gb, ob = g.render(), o.render()
+    assert len(gb) == len(ob) and gb == ob
+    assert list(g.body_offsets()) == list(o.body_offsets())
+    st = g.stats()
+    assert st["n_matched"] + st["n_dropped"] == s.n and st["n_dropped"] == f.n_nodes * (f.procs // 100)  # the orphans
+
+
+def test_fleet_replay_10m_samples_sampled_nodes_and_invariants(kgo):
+    """configs[3]: 2k nodes, 10M samples, full label set."""
+    f = Fleet.config(4)
+    g = kgx.Kgx(MODE_X)
+    g.set_table(f.table(MODE_X))
+    g.ingest(f.scrape(0))
+    body = np.empty(g.render_device() + 16, dtype=np.uint8)
+    n = g.render_into(body)
+    body = body[:n]
+    off = g.body_offsets()
+    assert off[0] == 0 and off[-1] == n and (np.diff(off.astype(np.int64)) > 0).all()
+    # every node's body is independent: the oracle renders a sample of nodes from a fleet of their own
+    for lo, cnt in ((0, 3), (997, 2), (1998, 2)):
+        sub = Fleet.config(4, n_nodes=cnt, node_base=lo)
+        o = kgo.Oracle(MODE_X, kgo.JOIN_HASH, 2)
+        o.set_table(sub.table(MODE_X))
+        o.ingest(sub.scrape(0))
+        want = o.render()
+        got = body[int(off[lo]):int(off[lo + cnt])].tobytes()
+        assert got == want, "bodies of nodes %d..%d differ" % (lo, lo + cnt)
+    # size-independent properties of the whole 3.3 GB text
+    st = g.stats()
+    n_lines = int(np.count_nonzero(body == 10))
+    assert n_lines == 6 * st["n_series"] + 2 * 6 * 2000            # 6 families x (series + HELP + TYPE per node)
+    assert st["n_matched"] == 9_900_000 and st["n_dropped"] == 100_000
+    starts = off[:-1].astype(np.int64)
+    assert (body[starts] == ord("#")).all() and body[-1] == 10
+    vals = g.read_values(3)                                         # pod_gpu_memory_usage = sum of used bytes
+    assert len(vals) == st["n_series"]
+    s = f.scrape(0)
+    orphan_free = float(vals.sum())
+    # linearity: the per-series sums add up to the sum over all joined samples (exact in u64, < 2^53 here)
+    pid_ok = np.ones(s.n, dtype=bool)
+    j = np.arange(f.procs)
+    # orphans are every 100th process index of each node before the shuffle: recover them by their PID not being in the table
+    tbl = f.table(MODE_X)
+    key_tbl = tbl.podkey_node[tbl.entry_podkey].astype(np.uint64) << np.uint64(32) | tbl.entry_pid.astype(np.uint64)
+    key_s = s.node.astype(np.uint64) << np.uint64(32) | s.pid.astype(np.uint64)
+    joined = np.isin(key_s, key_tbl)
+    assert int(joined.sum()) == st["n_matched"]
+    assert orphan_free == float(s.used[joined].sum(dtype=np.uint64))
+
+
+def test_time_window_60_scrapes_sum_max_last(kgo):
+    """configs[4]: 60 scrapes x 1M samples folded into one window, rendered once."""
+    f = Fleet.config(5)
+    t = f.table(MODE_X)
+    g, o = kgx.Kgx(MODE_X), kgo.Oracle(MODE_X, kgo.JOIN_HASH, THREADS)
+    g.set_table(t); o.set_table(t)
+    for k in range(f.scrapes):
+        s = f.scrape(k)
+        g.ingest(s); o.ingest(s)
+    gb, ob = g.render(), o.render()
+    assert gb == ob and len(gb) > 100_000_000
+    # idempotence: rendering again changes nothing; a new window starts empty
+    assert g.render() == gb
+    g.reset_window()
+    assert g.render() == b""
