@@ -13,6 +13,7 @@
 #include "../../include/kgx.h"
 #include "kgx_kernels.cuh"
 #include "kgx_render2.cuh"
+#include "kgx_render3.cuh"
 #include "kgx_ingest2.cuh"
 #include "kgx_table.hpp"
 
@@ -60,6 +61,7 @@ struct kgx_ctx {
   DBuf d_fam, d_tiles, d_tile_state, d_node_body_off, d_out;
   uint32_t n_tiles = 0, tile_lines = 0, render_smem = 0;
   bool render_v2 = false;  // second-generation writer (needs metric names of 15..64 bytes)
+  bool render_direct = false;  // ... in its direct-store variant (k_render3)
   RenderLayout lay{};
   int render_grid = 0, render_threads = 256;
   size_t last_len = 0;
@@ -172,19 +174,30 @@ DevAcc acc_view(kgx_ctx* c) {
 }
 int n_acc_arrays(const kgx_ctx* c) { return c->mode == KGX_MODE_X ? 6 : 3; }
 
-// the writer is compiled for three CTA sizes (= lines per tile)
-const void* render2_func(int threads) {
-  switch (threads) {
+// the writer is compiled for three CTA sizes (= lines per tile), staged (k_render2) or direct-store (k_render3)
+const void* render2_func(const kgx_ctx* c) {
+  if (c->render_direct) switch (c->render_threads) {
+    case 64: return reinterpret_cast<const void*>(&k_render3<64>);
+    case 128: return reinterpret_cast<const void*>(&k_render3<128>);
+    default: return reinterpret_cast<const void*>(&k_render3<256>);
+  }
+  switch (c->render_threads) {
     case 64: return reinterpret_cast<const void*>(&k_render2<64>);
     case 128: return reinterpret_cast<const void*>(&k_render2<128>);
     default: return reinterpret_cast<const void*>(&k_render2<256>);
   }
 }
 void launch_render2(kgx_ctx* c, int grid, const DevRender& R, unsigned long long* counters) {
+  const size_t sm = c->render_smem;
+  if (c->render_direct) switch (c->render_threads) {
+    case 64: k_render3<64><<<grid, 64, sm, c->stream>>>(R, c->lay, acc_view(c), counters); return;
+    case 128: k_render3<128><<<grid, 128, sm, c->stream>>>(R, c->lay, acc_view(c), counters); return;
+    default: k_render3<256><<<grid, 256, sm, c->stream>>>(R, c->lay, acc_view(c), counters); return;
+  }
   switch (c->render_threads) {
-    case 64: k_render2<64><<<grid, 64, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
-    case 128: k_render2<128><<<grid, 128, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
-    default: k_render2<256><<<grid, 256, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+    case 64: k_render2<64><<<grid, 64, sm, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+    case 128: k_render2<128><<<grid, 128, sm, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+    default: k_render2<256><<<grid, 256, sm, c->stream>>>(R, c->lay, acc_view(c), counters); break;
   }
 }
 
@@ -397,8 +410,9 @@ int upload_plan(kgx_ctx* c) {
   if (c->render_v2) {
     // per line: value slot + staged label + output text; 3 CTAs per SM when labels are short
     const uint64_t fixed = uint64_t(kMaxFamilies) * kNameStride + 64 + (64 + 16 + 128) + (max_header + 64);
-    const uint64_t per_line = kSlotBytes + p.max_label_len + max_line;
-    uint64_t budget = 74 * 1024;
+    c->render_direct = getenv("KGX_RENDER_DIRECT") != nullptr;  // k_render3: no output staging
+    const uint64_t per_line = kSlotBytes + p.max_label_len + (c->render_direct ? 0 : max_line);
+    uint64_t budget = c->render_direct ? 35 * 1024 : 74 * 1024;
     if (fixed + 16 * per_line > budget) budget = 200 * 1024;  // long labels: one CTA per SM
     if (fixed + per_line > budget) return fail(c, KGX_E_LIMIT, "label text too long for one render tile");
     if (const char* e = getenv("KGX_RENDER_THREADS")) c->render_threads = atoi(e);
@@ -409,10 +423,10 @@ int upload_plan(kgx_ctx* c) {
     c->lay.slots = up16(uint64_t(kMaxFamilies) * kNameStride);
     c->lay.stage = up16(c->lay.slots + uint64_t(c->render_threads) * kSlotBytes + 32);
     c->lay.out = up16(c->lay.stage + 32 + uint64_t(c->tile_lines) * p.max_label_len + 128 + 48);
-    c->lay.total = up16(c->lay.out + 16 + max_header + uint64_t(c->tile_lines) * max_line + 48);
+    c->lay.total = c->render_direct ? c->lay.out : up16(c->lay.out + 16 + max_header + uint64_t(c->tile_lines) * max_line + 48);
     c->render_smem = c->lay.total;
-    KGX_CUDA(c, cudaFuncSetAttribute(render2_func(c->render_threads), cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->render_smem)));
-    KGX_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, render2_func(c->render_threads), c->render_threads, c->render_smem));
+    KGX_CUDA(c, cudaFuncSetAttribute(render2_func(c), cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->render_smem)));
+    KGX_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, render2_func(c), c->render_threads, c->render_smem));
   } else {
     const uint64_t budget = 96 * 1024;
     if (max_line + max_header + 32 > budget) return fail(c, KGX_E_LIMIT, "label text too long for one render tile");
