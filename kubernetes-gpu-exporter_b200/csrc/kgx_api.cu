@@ -61,9 +61,10 @@ struct kgx_ctx {
   DBuf d_fam, d_tiles, d_tile_state, d_node_body_off, d_out;
   uint32_t n_tiles = 0, tile_lines = 0, render_smem = 0;
   bool render_v2 = false;  // second-generation writer (needs metric names of 15..64 bytes)
-  bool render_direct = false;  // ... in its direct-store variant (k_render3)
+  int render_kind = 1;         // 0 k_render2, 1 k_render3 direct stores, 2 k_render3 staged + TMA bulk store
+  bool render_direct = false;  // no output staging in shared memory (kind 1)
   RenderLayout lay{};
-  int render_grid = 0, render_threads = 256;
+  int render_grid = 0, render_threads = 64;   // measured best on B200: direct stores, 64-line tiles
   size_t last_len = 0;
   bool rendered = false;
   std::vector<FamMeta> fam;
@@ -174,31 +175,32 @@ DevAcc acc_view(kgx_ctx* c) {
 }
 int n_acc_arrays(const kgx_ctx* c) { return c->mode == KGX_MODE_X ? 6 : 3; }
 
-// the writer is compiled for three CTA sizes (= lines per tile), staged (k_render2) or direct-store (k_render3)
+// the writer is compiled for three CTA sizes (= lines per tile) and three data paths:
+// 0 k_render2 (late look-back, LSU flush), 1 k_render3 direct stores, 2 k_render3 staged + TMA bulk store
+#define KGX_RENDER_CASES(OP)                                                        \
+  switch (c->render_kind * 1000 + c->render_threads) {                              \
+    case 64: OP((k_render2<64>)); break;                                            \
+    case 128: OP((k_render2<128>)); break;                                          \
+    case 1032: OP((k_render3<32, false>)); break;                                   \
+    case 1064: OP((k_render3<64, false>)); break;                                   \
+    case 1128: OP((k_render3<128, false>)); break;                                  \
+    case 1256: OP((k_render3<256, false>)); break;                                  \
+    case 2064: OP((k_render3<64, true>)); break;                                    \
+    case 2128: OP((k_render3<128, true>)); break;                                   \
+    case 2256: OP((k_render3<256, true>)); break;                                   \
+    default: OP((k_render2<256>)); break;                                           \
+  }
 const void* render2_func(const kgx_ctx* c) {
-  if (c->render_direct) switch (c->render_threads) {
-    case 64: return reinterpret_cast<const void*>(&k_render3<64>);
-    case 128: return reinterpret_cast<const void*>(&k_render3<128>);
-    default: return reinterpret_cast<const void*>(&k_render3<256>);
-  }
-  switch (c->render_threads) {
-    case 64: return reinterpret_cast<const void*>(&k_render2<64>);
-    case 128: return reinterpret_cast<const void*>(&k_render2<128>);
-    default: return reinterpret_cast<const void*>(&k_render2<256>);
-  }
+  const void* f = nullptr;
+#define KGX_OP(K) f = reinterpret_cast<const void*>(&K)
+  KGX_RENDER_CASES(KGX_OP)
+#undef KGX_OP
+  return f;
 }
 void launch_render2(kgx_ctx* c, int grid, const DevRender& R, unsigned long long* counters) {
-  const size_t sm = c->render_smem;
-  if (c->render_direct) switch (c->render_threads) {
-    case 64: k_render3<64><<<grid, 64, sm, c->stream>>>(R, c->lay, acc_view(c), counters); return;
-    case 128: k_render3<128><<<grid, 128, sm, c->stream>>>(R, c->lay, acc_view(c), counters); return;
-    default: k_render3<256><<<grid, 256, sm, c->stream>>>(R, c->lay, acc_view(c), counters); return;
-  }
-  switch (c->render_threads) {
-    case 64: k_render2<64><<<grid, 64, sm, c->stream>>>(R, c->lay, acc_view(c), counters); break;
-    case 128: k_render2<128><<<grid, 128, sm, c->stream>>>(R, c->lay, acc_view(c), counters); break;
-    default: k_render2<256><<<grid, 256, sm, c->stream>>>(R, c->lay, acc_view(c), counters); break;
-  }
+#define KGX_OP(K) K<<<grid, c->render_threads, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters)
+  KGX_RENDER_CASES(KGX_OP)
+#undef KGX_OP
 }
 
 DevLabels labels_view(kgx_ctx* c) {
@@ -410,13 +412,15 @@ int upload_plan(kgx_ctx* c) {
   if (c->render_v2) {
     // per line: value slot + staged label + output text; 3 CTAs per SM when labels are short
     const uint64_t fixed = uint64_t(kMaxFamilies) * kNameStride + 64 + (64 + 16 + 128) + (max_header + 64);
-    c->render_direct = getenv("KGX_RENDER_DIRECT") != nullptr;  // k_render3: no output staging
+    if (const char* e = getenv("KGX_RENDER_KIND")) c->render_kind = atoi(e);
+    if (c->render_kind < 0 || c->render_kind > 2) c->render_kind = 1;
+    c->render_direct = c->render_kind == 1;
     const uint64_t per_line = kSlotBytes + p.max_label_len + (c->render_direct ? 0 : max_line);
     uint64_t budget = c->render_direct ? 35 * 1024 : 74 * 1024;
     if (fixed + 16 * per_line > budget) budget = 200 * 1024;  // long labels: one CTA per SM
     if (fixed + per_line > budget) return fail(c, KGX_E_LIMIT, "label text too long for one render tile");
     if (const char* e = getenv("KGX_RENDER_THREADS")) c->render_threads = atoi(e);
-    if (c->render_threads != 64 && c->render_threads != 128 && c->render_threads != 256) c->render_threads = 256;
+    if (c->render_threads != 64 && c->render_threads != 128 && c->render_threads != 256 && !(c->render_threads == 32 && c->render_kind == 1)) c->render_threads = 64;
     c->tile_lines = uint32_t(std::min<uint64_t>(uint64_t(c->render_threads), (budget - fixed) / per_line));
     auto up16 = [](uint64_t v) { return uint32_t((v + 15) & ~15ull); };
     c->lay.names = 0;

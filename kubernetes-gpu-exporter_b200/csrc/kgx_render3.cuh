@@ -19,7 +19,7 @@ __device__ __forceinline__ void stg128_cs(uint8_t* p, uint4 v) {
   asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
-template <int THREADS>
+template <int THREADS, bool STAGE>
 __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout lay, DevAcc acc, unsigned long long* counters) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ unsigned long long s_scan[THREADS / 32];
@@ -36,8 +36,8 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
     const uint32_t f = i / kNameStride, o = i % kNameStride;
     smem[lay.names + i] = (o >= 16 && o < 16 + 64 && f < R.n_families) ? R.fam[f].name[o - 16] : uint8_t('#');
   }
-  if (tid < 64) {
-    const uint32_t e = tid >> 2, w = tid & 3;
+  for (uint32_t i = tid; i < 64; i += THREADS) {
+    const uint32_t e = i >> 2, w = i & 3;
     const int n = int(e) - int(4 * w);
     s_mask[e][w] = n <= 0 ? 0u : (n >= 4 ? 0xffffffffu : ((1u << (8 * n)) - 1u));
   }
@@ -74,7 +74,10 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
   uint32_t parity = 0;
   for (;;) {
     const uint32_t t = s_next;
-    if (t >= R.n_tiles) return;
+    if (t >= R.n_tiles) {
+      if (STAGE && tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // my bulk stores have landed
+      return;
+    }
     const Tile tile = s_desc;
     const unsigned long long g0 = s_g0;
     const FamMeta& fm = R.fam[tile.family];
@@ -103,6 +106,7 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
     unsigned long long inc = mine;
     for (int o = 1; o < 32; o <<= 1) { unsigned long long u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
     if (lane == 31) s_scan[wid] = inc;
+    if (STAGE && tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // last tile's bulk store has read the tile buffer
     __syncthreads();  // (1) also: everyone has read s_next / s_desc / s_g0
     unsigned long long woff = 0, all = 0;
     for (int k = 0; k < THREADS / 32; ++k) { if (k < int(wid)) woff += s_scan[k]; all += s_scan[k]; }
@@ -139,18 +143,19 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
     uint8_t* gtile = R.out + base;                    // first byte of the tile in the output
     uint8_t* galn = R.out + (base & ~15ull);          // 16-aligned origin: position v lives at galn + v
     const uint32_t sh = uint32_t(base & 15);
-    if (hdr) for (uint32_t i = tid; i < hdr; i += THREADS) gtile[i] = fm.header[i];
+    const uint32_t outb = sm0 + lay.out;  // STAGE: position v lives at outb + v in shared memory
+    if (!STAGE && hdr) for (uint32_t i = tid; i < hdr; i += THREADS) gtile[i] = fm.header[i];
     mbar_wait(bar, parity);  // staged labels have landed (issued a whole tile ago)
     parity ^= 1;
     // ---- pass 2: stream my line to the output as 16-byte chunks aligned to the global address
     if (live) {
       const uint32_t g = sh + off;                                              // first byte of my line (position)
       const uint32_t b0 = g + name_len, b1 = b0 + lbl_len, b2 = b1 + vlen + 2;  // source boundaries; b2 = line end
-      const uint32_t start = (g + 15u) & ~15u;
-      const uint32_t stop = last_live ? (b2 & ~15u) : ((b2 + 15u) & ~15u);      // my full chunks: [start, stop)
+      const uint32_t start = (STAGE && first_live) ? (g & ~15u) : ((g + 15u) & ~15u);
+      const uint32_t stop = (!STAGE && last_live) ? (b2 & ~15u) : ((b2 + 15u) & ~15u);  // my chunks: [start, stop)
       const uint32_t name_sm = sm0 + lay.names + tile.family * kNameStride + 16;
       const uint32_t d0 = name_sm - g, d1 = lbl_src - b0, d2 = slot - b1, d3 = name_sm - b2;  // source = position + delta
-      if (first_live) {  // the bytes before my first aligned chunk: nobody else writes them
+      if (!STAGE && first_live) {  // the bytes before my first aligned chunk: nobody else writes them
         for (uint32_t q = g; q < start && q < b2; ++q) galn[q] = smem[lay.names + tile.family * kNameStride + 16 + (q - g)];
       }
       uint32_t p = start, e = 0;
@@ -159,9 +164,13 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
         const uint4 nw = gather16(p + d);
         a4 = e ? merge16(a4, nw, e, mask_sm) : nw;
         if (b >= p + 16) {
-          stg128_cs(galn + p, a4);
+          if (STAGE) sts128(outb + p, a4); else stg128_cs(galn + p, a4);
           p += 16;
-          while (p + 16 <= b) { stg128_cs(galn + p, gather16(p + d)); p += 16; }
+          while (p + 16 <= b) {
+            const uint4 c4 = gather16(p + d);
+            if (STAGE) sts128(outb + p, c4); else stg128_cs(galn + p, c4);
+            p += 16;
+          }
           a4 = gather16(p + d);
         }
         e = b - p;
@@ -169,7 +178,7 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
       append(d0, b0);  // metric name
       append(d1, b1);  // labels
       append(d2, b2);  // " <value>\n"
-      if (!last_live) {
+      if (STAGE || !last_live) {
         append(d3, stop);  // the head of the next line's name completes my last chunk
       } else if (e) {      // the tile ends inside a chunk: its bytes belong to me, the rest to the next tile
         s_tail = a4;  // one thread per tile gets here: park the chunk, then byte-copy
@@ -178,8 +187,25 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
       }
     }
     __syncthreads();  // (2) label stage and value slots are free
+    if (STAGE) {
+      if (hdr) for (uint32_t i = tid; i < hdr; i += THREADS) smem[lay.out + sh + i] = fm.header[i];
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // my writes to the tile buffer -> visible to the bulk store
+    }
     if (wid == 0) fetch_next();  // next ticket, descriptor, label copy
     __syncthreads();  // (3) s_next / s_desc / s_g0 visible
+    if (STAGE) {  // the tile leaves: byte head, one TMA bulk store for the 16-byte aligned body, byte tail
+      const uint32_t head = min(total, (16u - sh) & 15u);
+      const uint32_t body = (total - head) & ~15u;
+      if (tid == 0 && body) {
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gtile + head), "r"(outb + sh + head), "r"(body) : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+      if (tid >= 32 && tid < 32 + head) gtile[tid - 32] = smem[lay.out + sh + tid - 32];
+      if (tid >= 48 && tid < 48 + (total - head - body)) {
+        const uint32_t i = head + body + tid - 48;
+        gtile[i] = smem[lay.out + sh + i];
+      }
+    }
   }
 }
 
