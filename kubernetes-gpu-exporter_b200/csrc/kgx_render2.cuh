@@ -64,7 +64,12 @@ __device__ __forceinline__ uint4 gather16(uint32_t a) {
 // bytes [0,e) from lo, bytes [e,16) from hi (0 < e < 16); mask_sm: shared table of
 // 16 byte masks, entry e = the first e bytes set
 __device__ __forceinline__ uint4 merge16(uint4 lo, uint4 hi, uint32_t e, uint32_t mask_sm) {
-  const uint4 m = lds128(mask_sm + 16u * e);
+  (void)mask_sm;  // masks are computed: the shared-memory pipe is the writer's bottleneck, the ALU is not
+  auto mk = [e](int w) -> uint32_t {  // the bytes of word w that are < e
+    const int n = min(max(int(e) - 4 * w, 0), 4);
+    return __funnelshift_rc(0xffffffffu, 0u, uint32_t(32 - 8 * n));
+  };
+  const uint4 m = make_uint4(mk(0), mk(1), mk(2), mk(3));
   return make_uint4((lo.x & m.x) | (hi.x & ~m.x), (lo.y & m.y) | (hi.y & ~m.y), (lo.z & m.z) | (hi.z & ~m.z),
                     (lo.w & m.w) | (hi.w & ~m.w));
 }

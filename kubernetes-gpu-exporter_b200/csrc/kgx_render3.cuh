@@ -161,17 +161,28 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
       uint32_t p = start, e = 0;
       uint4 a4 = make_uint4(0, 0, 0, 0);
       auto append = [&](uint32_t d, uint32_t b) {  // source = position + d, up to position b (exclusive)
-        const uint4 nw = gather16(p + d);
+        // the source is walked in 16-byte steps: four new words per step, the fifth carried over
+        uint32_t wa = (p + d) & ~3u;
+        const uint32_t r = ((p + d) & 3u) * 8u;
+        uint32_t w0 = lds32(wa), w1 = lds32(wa + 4), w2 = lds32(wa + 8), w3 = lds32(wa + 12), w4 = lds32(wa + 16);
+        auto chunk = [&]() {
+          return make_uint4(__funnelshift_r(w0, w1, r), __funnelshift_r(w1, w2, r), __funnelshift_r(w2, w3, r),
+                            __funnelshift_r(w3, w4, r));
+        };
+        auto step = [&]() { wa += 16; w0 = w4; w1 = lds32(wa + 4); w2 = lds32(wa + 8); w3 = lds32(wa + 12); w4 = lds32(wa + 16); };
+        const uint4 nw = chunk();
         a4 = e ? merge16(a4, nw, e, mask_sm) : nw;
         if (b >= p + 16) {
           if (STAGE) sts128(outb + p, a4); else stg128_cs(galn + p, a4);
           p += 16;
+          step();
           while (p + 16 <= b) {
-            const uint4 c4 = gather16(p + d);
+            const uint4 c4 = chunk();
             if (STAGE) sts128(outb + p, c4); else stg128_cs(galn + p, c4);
             p += 16;
+            step();
           }
-          a4 = gather16(p + d);
+          a4 = chunk();
         }
         e = b - p;
       };
