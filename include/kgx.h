@@ -177,6 +177,23 @@ int kgx_ingest(kgx_ctx* ctx, const kgx_cols* cols);
  * ctx's GPU (no host<->device copy).  Used to time the device pipeline. */
 int kgx_ingest_device(kgx_ctx* ctx, const kgx_cols* cols);
 
+/* R modes: ingest straight from what NVML hands back, without building columns
+ * on the host.  `infos` is every device's nvmlProcessInfo_t array
+ * (DeviceGetComputeRunningProcesses, main.go:135; struct at nvml.h:294-303)
+ * concatenated in the loop order of main.go:123 — node 0 device 0, node 0
+ * device 1, ... — and dev_off[node*G+gpu] .. dev_off[node*G+gpu+1] is the row
+ * range of one device (n_nodes*G+1 entries); gpu_total as in kgx_cols.  The
+ * library unpacks on the GPU and then runs the same join as kgx_ingest. */
+typedef struct kgx_nvml_process_info {  /* = nvmlProcessInfo_t, 24 bytes */
+  uint32_t pid;
+  uint32_t pad_;
+  uint64_t used_gpu_memory;
+  uint32_t gpu_instance_id;
+  uint32_t compute_instance_id;
+} kgx_nvml_process_info;
+int kgx_ingest_nvml(kgx_ctx* ctx, const kgx_nvml_process_info* infos, const uint64_t* dev_off,
+                    const uint64_t* gpu_total);
+
 /* X mode: start a new aggregation window (forget sums/max/last/count).
  * No-op error KGX_E_STATE in R modes, whose series never reset. */
 int kgx_reset_window(kgx_ctx* ctx);

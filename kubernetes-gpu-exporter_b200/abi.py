@@ -11,6 +11,10 @@ MODE_R_INTENDED, MODE_R_LITERAL, MODE_X = 0, 1, 2
 K_INGEST, K_FINALIZE, K_INDEX, K_RENDER, K_OTHER, K_COUNT = 0, 1, 2, 3, 4, 5
 K_NAMES = ["ingest", "finalize", "index", "render", "other"]
 
+# nvmlProcessInfo_t (nvml.h:294-303): 24 bytes
+NVML_PROCESS_INFO = np.dtype([("pid", "<u4"), ("pad_", "<u4"), ("used_gpu_memory", "<u8"),
+                              ("gpu_instance_id", "<u4"), ("compute_instance_id", "<u4")])
+
 u32p = C.POINTER(C.c_uint32)
 u64p = C.POINTER(C.c_uint64)
 

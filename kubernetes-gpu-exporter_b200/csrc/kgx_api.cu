@@ -667,6 +667,43 @@ int kgx_ingest(kgx_ctx* c, const kgx_cols* cols) {
   return ingest_device_locked(c, &d);
 }
 
+int kgx_ingest_nvml(kgx_ctx* c, const kgx_nvml_process_info* infos, const uint64_t* dev_off, const uint64_t* gpu_total) {
+  if (!c) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  if (c->mode == KGX_MODE_X) return fail(c, KGX_E_STATE, "kgx_ingest_nvml: nvmlProcessInfo_t carries no utilisation or timestamp; R modes only");
+  if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_ingest_nvml before kgx_set_table");
+  if (!dev_off || !gpu_total) return fail(c, KGX_E_INVAL, "kgx_ingest_nvml: dev_off / gpu_total missing");
+  static_assert(sizeof(kgx_nvml_process_info) == 24 && sizeof(NvmlProcessInfo) == 24, "nvmlProcessInfo_t is 24 bytes");
+  const uint32_t n_dev = c->plan.n_nodes * c->plan.G;
+  const size_t n = size_t(dev_off[n_dev]);
+  if (dev_off[0] != 0) return fail(c, KGX_E_INVAL, "kgx_ingest_nvml: dev_off[0] must be 0");
+  for (uint32_t d = 0; d < n_dev; ++d)
+    if (dev_off[d + 1] < dev_off[d]) return fail(c, KGX_E_INVAL, "kgx_ingest_nvml: dev_off not ascending");
+  if (n && !infos) return fail(c, KGX_E_INVAL, "kgx_ingest_nvml: infos missing");
+  KGX_TRY(dev_reserve(c, c->d_tmp[1], n * 24));
+  KGX_TRY(dev_reserve(c, c->d_tmp[2], (size_t(n_dev) + 1) * 8));
+  const size_t bytes[8] = {n * 4, n * 4, n * 8, n * 4, 0, 0, 0, (size_t(c->plan.n_nodes) + 1) * 8};
+  for (int k : {0, 1, 2, 3, 7}) KGX_TRY(dev_reserve(c, c->d_cols[k], bytes[k]));
+  if (n) KGX_CUDA(c, cudaMemcpyAsync(c->d_tmp[1].p, infos, n * 24, cudaMemcpyHostToDevice, c->stream));
+  KGX_CUDA(c, cudaMemcpyAsync(c->d_tmp[2].p, dev_off, (size_t(n_dev) + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+  {
+    Timed tm(c, KGX_K_OTHER);
+    if (n) k_unpack_nvml<<<cdiv(n, 256), 256, 0, c->stream>>>(ptr<NvmlProcessInfo>(c->d_tmp[1]), ptr<unsigned long long>(c->d_tmp[2]), n_dev,
+                                                           c->plan.G, n, ptr<uint32_t>(c->d_cols[0]), ptr<uint32_t>(c->d_cols[1]),
+                                                           ptr<uint32_t>(c->d_cols[3]), ptr<unsigned long long>(c->d_cols[2]));
+    k_node_off_from_dev_off<<<cdiv(c->plan.n_nodes + 1, 256), 256, 0, c->stream>>>(ptr<unsigned long long>(c->d_tmp[2]), c->plan.n_nodes,
+                                                                                  c->plan.G, ptr<unsigned long long>(c->d_cols[7]));
+    tm.launches(n ? 2 : 1);
+    KGX_TRY(launch_check(c, "k_unpack_nvml"));
+  }
+  kgx_cols d{};
+  d.n = n;
+  d.pid = ptr<uint32_t>(c->d_cols[0]); d.gpu = ptr<uint32_t>(c->d_cols[1]); d.used = ptr<uint64_t>(c->d_cols[2]);
+  d.node = ptr<uint32_t>(c->d_cols[3]); d.node_off = ptr<uint64_t>(c->d_cols[7]); d.gpu_total = gpu_total;
+  return ingest_device_locked(c, &d);
+}
+
 int kgx_reset_window(kgx_ctx* c) {
   if (!c) return KGX_E_INVAL;
   std::lock_guard<std::mutex> g(c->mu);

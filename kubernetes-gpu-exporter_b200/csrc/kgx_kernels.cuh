@@ -458,6 +458,23 @@ __global__ void k_values(DevRender R, DevAcc acc, int kind, uint32_t n_series, d
   live_out[r] = live;
 }
 
+// ---- NVML wire format -> columns (R modes) ------------------------------------------------
+struct NvmlProcessInfo { uint32_t pid, pad_; unsigned long long used; uint32_t gi, ci; };  // nvml.h:294-303
+// one thread per row: which device (node*G+gpu) owns it, then scatter into the columns
+__global__ void k_unpack_nvml(const NvmlProcessInfo* infos, const unsigned long long* dev_off, uint32_t n_dev, uint32_t G,
+                              uint64_t n, uint32_t* pid, uint32_t* gpu, uint32_t* node, unsigned long long* used) {
+  const uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
+  if (i >= n) return;
+  uint32_t lo = 0, hi = n_dev;  // last device with dev_off <= i
+  while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (dev_off[mid] <= i) lo = mid; else hi = mid; }
+  const NvmlProcessInfo p = infos[i];
+  pid[i] = p.pid; used[i] = p.used; gpu[i] = lo % G; node[i] = lo / G;
+}
+__global__ void k_node_off_from_dev_off(const unsigned long long* dev_off, uint32_t n_nodes, uint32_t G, unsigned long long* node_off) {
+  const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n <= n_nodes) node_off[n] = dev_off[size_t(n) * G];
+}
+
 // ---- float printer entry (tests) ---------------------------------------------------------
 __global__ void k_format_values(const double* v, uint64_t n, uint8_t* out32) {
   const uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;

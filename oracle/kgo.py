@@ -109,9 +109,14 @@ class Oracle:
     def reset_window(self):
         self._chk(lib().kgo_reset_window(self._h))
 
-    def render(self):
+    def render(self, copy=True):
+        """The body as bytes; with copy=False only its length (bodies beyond 2 GB)."""
         p, n = C.c_void_p(), C.c_size_t()
         self._chk(lib().kgo_render(self._h, C.byref(p), C.byref(n)))
+        if not copy:
+            return n.value
+        if n.value >= 1 << 31:
+            return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(n.value,)).tobytes()
         return C.string_at(p.value, n.value) if n.value else b""
 
     def body_offsets(self):

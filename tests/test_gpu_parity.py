@@ -244,3 +244,27 @@ def test_long_labels_and_many_lines_per_tile(kgo):
     c = _cols([(1000 + i, i % 8, (i + 1) * 12345678901) for i in range(300)])
     g.ingest(c); o.ingest(c)
     _same(g, o)
+
+
+def test_ingest_from_nvml_process_info_arrays(kgo):
+    """The NVML wire format (nvmlProcessInfo_t arrays per device, main.go:135) gives the same body as columns."""
+    from kgx_b200 import abi
+    f = Fleet(n_nodes=5, pods=30, procs=200, seed=0xB200 + 2)
+    t = f.table(MODE_R_INTENDED)
+    s = f.scrape(0, x_cols=False)
+    # regroup the samples the way the reference's loops see them: node, then device, then process order
+    order = np.lexsort((np.arange(s.n), s.gpu, s.node))
+    dev = s.node[order].astype(np.int64) * f.G + s.gpu[order]
+    dev_off = np.zeros(f.n_nodes * f.G + 1, dtype=np.uint64)
+    dev_off[1:] = np.cumsum(np.bincount(dev, minlength=f.n_nodes * f.G))
+    infos = np.zeros(s.n, dtype=abi.NVML_PROCESS_INFO)
+    infos["pid"], infos["used_gpu_memory"] = s.pid[order], s.used[order]
+    infos["gpu_instance_id"] = 0xFFFFFFFF
+    g, o = _pair(kgo, MODE_R_INTENDED)
+    g.set_table(t); o.set_table(t)
+    g.ingest_nvml(infos, dev_off, s.gpu_total)
+    o.ingest(Cols(pid=s.pid[order], gpu=s.gpu[order], used=s.used[order], node=s.node[order], gpu_total=s.gpu_total))
+    assert len(_same(g, o)) > 0
+    gx = kgx.Kgx(MODE_X)
+    with pytest.raises(kgx.KgxError):
+        gx.ingest_nvml(infos, dev_off, s.gpu_total)
