@@ -43,6 +43,25 @@ UNIT = "samples/s"
 CFG = 4
 
 
+def ncu_traffic(kernel_csv):
+    """dram read+write bytes per launch of the dominant kernel, from the committed
+    `ncu --set full` raw page (profiles/); None if the capture is not there."""
+    import csv
+    path = os.path.join(ROOT, "profiles", kernel_csv)
+    if not os.path.exists(path):
+        return None
+    rows = list(csv.reader(open(path)))
+    hdr, units, vals = rows[0], rows[1], rows[-1]
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    total = 0.0
+    for key in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+        if key not in hdr:
+            return None
+        i = hdr.index(key)
+        total += float(vals[i].replace(",", "")) * scale.get(units[i], 1.0)
+    return total
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -251,8 +270,9 @@ def main():
     alg_render = n_fam * label_bytes + body_len
     achieved = alg_render / (render_ms * 1e-3) / 1e9 if render_ms > 0 else 0.0
     alg_pipeline = cols.n * 36 + len(table.entry_pid) * 12 + alg_render
-    roofline = {"bound": "hbm", "kernel": "k_render", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+    roofline = {"bound": "hbm", "kernel": "k_render3<64,false> (exposition writer)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": ncu_traffic("r01_k_render3_raw.csv"), "peak_source": peak_src,
+                "traffic_source": "profiles/r01_k_render3_raw.csv (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, one launch)",
                 "algorithmic_bytes_per_launch": alg_render, "kernel_ms": render_ms,
                 "share_of_step": render_ms / ms if ms else None,
                 "pipeline": {"algorithmic_bytes_per_step": alg_pipeline, "achieved_gbs": alg_pipeline / (ms * 1e-3) / 1e9,
