@@ -525,6 +525,7 @@ int render_device_locked(kgx_ctx* c, size_t* len) {
   R.fam = ptr<FamMeta>(c->d_fam); R.n_families = uint32_t(c->fam.size());
   R.tiles = ptr<Tile>(c->d_tiles); R.n_tiles = c->n_tiles;
   R.lbl_off = ptr<unsigned long long>(c->d_lbl_off); R.lbl_blob = ptr<uint8_t>(c->d_lbl_blob);
+  R.ser_len = ptr<uint32_t>(c->d_ser_len);
   R.ser_gidx = ptr<uint32_t>(c->d_ser_gidx); R.gpu_total = ptr<unsigned long long>(c->d_gpu_total);
   R.tile_state = ptr<unsigned long long>(c->d_tile_state); R.node_body_off = ptr<unsigned long long>(c->d_node_body_off);
   R.out = ptr<uint8_t>(c->d_out); R.smem_bytes = c->render_smem;
@@ -972,6 +973,7 @@ extern "C" int kgx_render_noalloc(kgx_ctx* c, uint8_t* d_out, size_t cap, size_t
   R.fam = ptr<FamMeta>(c->d_fam); R.n_families = uint32_t(c->fam.size());
   R.tiles = ptr<Tile>(c->d_tiles); R.n_tiles = c->n_tiles;
   R.lbl_off = ptr<unsigned long long>(c->d_lbl_off); R.lbl_blob = ptr<uint8_t>(c->d_lbl_blob);
+  R.ser_len = ptr<uint32_t>(c->d_ser_len);
   R.ser_gidx = ptr<uint32_t>(c->d_ser_gidx); R.gpu_total = ptr<unsigned long long>(c->d_gpu_total);
   R.tile_state = scratch + C_COUNT;
   R.node_body_off = scratch + C_COUNT + kNoallocMaxTiles;

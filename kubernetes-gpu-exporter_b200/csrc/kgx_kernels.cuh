@@ -331,6 +331,7 @@ struct DevRender {
   const Tile* tiles;
   uint32_t n_tiles;
   const unsigned long long* lbl_off;  // [n_series+1]
+  const uint32_t* ser_len;            // [n_series] label bytes of each series
   const uint8_t* lbl_blob;
   const uint32_t* ser_gidx;
   const unsigned long long* gpu_total;  // X: [n_nodes*G]

@@ -28,7 +28,7 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
   __shared__ __align__(16) uint32_t s_mask[16][4];
   __shared__ uint32_t s_next;
   __shared__ Tile s_desc;
-  __shared__ unsigned long long s_g0;
+  __shared__ uint32_t s_l0;  // where the tile's first label starts inside the staged range
   const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const uint32_t sm0 = uint32_t(__cvta_generic_to_shared(smem));
   const uint32_t bar = uint32_t(__cvta_generic_to_shared(&s_bar));
@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
         asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
       }
       s_desc = d;
-      s_g0 = g0;
+      s_l0 = uint32_t(L0 - g0);
     }
     if (lane == 0) s_next = nt;
   };
@@ -79,30 +79,29 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
       return;
     }
     const Tile tile = s_desc;
-    const unsigned long long g0 = s_g0;
+    const uint32_t l0 = s_l0;
     const FamMeta& fm = R.fam[tile.family];
     const uint32_t name_len = fm.name_len;
     // ---- pass 1: value text and exact length of my line
     const uint32_t slot = sm0 + lay.slots + tid * kSlotBytes;
-    uint32_t len = 0, lbl_len = 0, vlen = 0, lbl_src = 0;
+    uint32_t len = 0, lbl_len = 0, vlen = 0;
     bool live = false;
     if (tid < tile.count) {
       const uint32_t r = tile.first + tid;
+      lbl_len = R.ser_len[r];  // 4 bytes per series; offsets inside the tile come from the CTA scan below
       const double v = series_value(fm.kind, acc, R, r, live);
       if (live) {
         uint8_t* sp = smem + lay.slots + tid * kSlotBytes;
         sp[0] = ' ';
         vlen = uint32_t(format_value(v, sp + 1));
         sp[1 + vlen] = '\n';
-        const unsigned long long at = R.lbl_off[r];
-        lbl_len = uint32_t(R.lbl_off[r + 1] - at);
-        lbl_src = sm0 + lay.stage + 32 + uint32_t(at - g0);
         len = name_len + lbl_len + vlen + 2;
       }
     }
     const uint32_t hdr = ((tile.flags & 1) && acc.node_live[tile.node] != 0) ? fm.header_len : 0;
-    // ---- exclusive scan over the CTA: low word = bytes, high word = live lines
-    const unsigned long long mine = (uint64_t(live) << 32) | len;
+    // ---- exclusive scan over the CTA, three fields at once: output bytes (24 bits), label bytes of
+    // every series, printed or not (24 bits), lines printed (16 bits)
+    const unsigned long long mine = (uint64_t(live) << 48) | (uint64_t(lbl_len) << 24) | len;
     unsigned long long inc = mine;
     for (int o = 1; o < 32; o <<= 1) { unsigned long long u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
     if (lane == 31) s_scan[wid] = inc;
@@ -111,10 +110,11 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
     unsigned long long woff = 0, all = 0;
     for (int k = 0; k < THREADS / 32; ++k) { if (k < int(wid)) woff += s_scan[k]; all += s_scan[k]; }
     const unsigned long long exc = woff + inc - mine;
-    const uint32_t off = hdr + uint32_t(exc);
-    const uint32_t total = hdr + uint32_t(all);
-    const bool first_live = live && uint32_t(exc >> 32) == 0;
-    const bool last_live = live && uint32_t(exc >> 32) + 1 == uint32_t(all >> 32);
+    const uint32_t off = hdr + (uint32_t(exc) & 0xffffffu);
+    const uint32_t total = hdr + (uint32_t(all) & 0xffffffu);
+    const uint32_t lbl_src = sm0 + lay.stage + 32 + l0 + (uint32_t(exc >> 24) & 0xffffffu);  // my label in the staged range
+    const bool first_live = live && uint32_t(exc >> 48) == 0;
+    const bool last_live = live && uint32_t(exc >> 48) + 1 == uint32_t(all >> 48);
     // ---- global byte offset of the tile: decoupled look-back, 32 predecessors per step.
     // Every warp resolves it for itself (same loads, same answer): no barrier, no broadcast.
     if (tid == 0 && t > 0) atomicExch(&R.tile_state[t], kStAgg | total);
