@@ -234,6 +234,17 @@ int kgx_render(kgx_ctx* ctx, uint8_t* out, size_t cap, size_t* len);
 #define KGX_NOALLOC_SCRATCH_BYTES ((8 + KGX_NOALLOC_MAX_TILES + KGX_NOALLOC_MAX_NODES + 1) * 8) /* 163 912 */
 int kgx_render_noalloc(kgx_ctx* ctx, uint8_t* d_out, size_t cap, size_t* len);
 
+/* Split form of kgx_render for a pipelined exporter: kgx_render_begin renders,
+ * returns the size, and STARTS the device->host copy of the body into `out`
+ * (pinned memory from kgx_host_alloc, or the copy cannot overlap) on a second
+ * stream; kgx_render_end waits until the bytes are in `out`.  Between the two
+ * the caller may already kgx_reset_window / kgx_ingest the next scrape: its
+ * host->device copies and kernels overlap the outgoing body on the full-duplex
+ * link.  The next render (or table change) waits for a copy still in flight.
+ * The reference serves a scrape and polls concurrently too (main.go:68-72). */
+int kgx_render_begin(kgx_ctx* ctx, uint8_t* out, size_t cap, size_t* len);
+int kgx_render_end(kgx_ctx* ctx);
+
 /* Device pointer and size of the last rendered text (valid until the next
  * render on this ctx); for peer copies / NCCL gathers of bodies. */
 int kgx_body_device(kgx_ctx* ctx, const uint8_t** dptr, size_t* len);

@@ -34,6 +34,9 @@ struct kgx_ctx {
   int device = 0, mode = 0;
   bool profile = false, own_stream = false;
   cudaStream_t stream = nullptr;
+  cudaStream_t copy_stream = nullptr;  // kgx_render_begin: body D2H overlaps the next ingest
+  cudaEvent_t ev_rendered = nullptr;
+  bool copy_pending = false;
   std::mutex mu;
   std::string err;
   int sm_count = 148;
@@ -137,6 +140,11 @@ struct Timed {  // CUDA-event bracket around a launch sequence when profiling
   }
 };
 
+// a body copy started by kgx_render_begin still reads d_out: finish it before d_out is rewritten or freed
+void wait_copy(kgx_ctx* c) {
+  if (c->copy_pending) { cudaStreamSynchronize(c->copy_stream); c->copy_pending = false; }
+}
+
 int launch_check(kgx_ctx* c, const char* what) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { c->err = std::string(what) + ": " + cudaGetErrorString(e); return KGX_E_CUDA; }
@@ -233,6 +241,7 @@ void build_family_meta(kgx_ctx* c) {
 // Merge the pending slots into the series index, re-rank every series, move
 // the per-series state to the new ranks, re-materialise label text and tiles.
 int rebuild_index(kgx_ctx* c) {
+  wait_copy(c);
   Timed tm(c, KGX_K_INDEX);
   const uint32_t nw = c->n_words;
   const uint32_t old_n = c->n_series;
@@ -329,6 +338,7 @@ int rebuild_index(kgx_ctx* c) {
 }
 
 void free_table_state(kgx_ctx* c) {
+  wait_copy(c);
   DBuf* all[] = {&c->d_node_a_base, &c->d_node_tab, &c->d_tab, &c->d_pk_slot0, &c->d_pk_stride, &c->d_grank, &c->d_node_slot_base,
                  &c->d_A_blob, &c->d_B_blob, &c->d_G_blob, &c->d_A_off, &c->d_B_off, &c->d_G_off, &c->d_runs,
                  &c->d_bm, &c->d_pending, &c->d_popc, &c->d_prefix, &c->d_ser_slot, &c->d_ser_a, &c->d_ser_gidx,
@@ -512,6 +522,7 @@ int ingest_device_locked(kgx_ctx* c, const kgx_cols* s) {
 }
 
 int render_device_locked(kgx_ctx* c, size_t* len) {
+  wait_copy(c);
   if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_render before kgx_set_table");
   if (c->n_tiles == 0) { c->last_len = 0; c->rendered = true; if (len) *len = 0; c->stats.rendered_bytes = 0; return KGX_OK; }
   unsigned long long* ctr = ptr<unsigned long long>(c->d_counters);
@@ -586,12 +597,15 @@ void kgx_destroy(kgx_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
+  wait_copy(c);
   free_table_state(c);
   dev_free(c, c->d_fam); dev_free(c, c->d_counters); dev_free(c, c->d_block_sums);
   for (auto& b : c->d_cols) dev_free(c, b);
   for (auto& b : c->d_tmp) dev_free(c, b);
   for (auto& r : c->regions) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
   if (c->h_counters) cudaFreeHost(c->h_counters);
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+  if (c->ev_rendered) cudaEventDestroy(c->ev_rendered);
   if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -736,6 +750,37 @@ int kgx_render(kgx_ctx* c, uint8_t* out, size_t cap, size_t* len) {
     if (!out) return fail(c, KGX_E_INVAL, "null output buffer");
     KGX_CUDA(c, cudaMemcpyAsync(out, c->d_out.p, *len, cudaMemcpyDeviceToHost, c->stream));
     KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
+  return KGX_OK;
+}
+
+int kgx_render_begin(kgx_ctx* c, uint8_t* out, size_t cap, size_t* len) {
+  if (!c || !len) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  KGX_TRY(render_device_locked(c, len));
+  if (*len > cap) return fail(c, KGX_E_NOSPACE, "output buffer too small");
+  if (*len) {
+    if (!out) return fail(c, KGX_E_INVAL, "null output buffer");
+    if (!c->copy_stream) {
+      KGX_CUDA(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+      KGX_CUDA(c, cudaEventCreateWithFlags(&c->ev_rendered, cudaEventDisableTiming));
+    }
+    KGX_CUDA(c, cudaEventRecord(c->ev_rendered, c->stream));
+    KGX_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_rendered, 0));
+    KGX_CUDA(c, cudaMemcpyAsync(out, c->d_out.p, *len, cudaMemcpyDeviceToHost, c->copy_stream));
+    c->copy_pending = true;
+  }
+  return KGX_OK;
+}
+
+int kgx_render_end(kgx_ctx* c) {
+  if (!c) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  if (c->copy_pending) {
+    KGX_CUDA(c, cudaStreamSynchronize(c->copy_stream));
+    c->copy_pending = false;
   }
   return KGX_OK;
 }

@@ -15,7 +15,7 @@ _LIB = None
 
 EXPORTS = [
     "kgx_abi_version", "kgx_strerror", "kgx_last_error", "kgx_create", "kgx_destroy", "kgx_set_table", "kgx_ingest",
-    "kgx_ingest_device", "kgx_ingest_nvml", "kgx_reset_window", "kgx_render_device", "kgx_render", "kgx_body_device", "kgx_body_offsets",
+    "kgx_ingest_device", "kgx_ingest_nvml", "kgx_reset_window", "kgx_render_device", "kgx_render", "kgx_render_begin", "kgx_render_end", "kgx_body_device", "kgx_body_offsets",
     "kgx_read_values", "kgx_family_count", "kgx_family_info", "kgx_slot_labels", "kgx_format_values", "kgx_host_alloc",
     "kgx_host_free", "kgx_get_stats", "kgx_get_profile", "kgx_profile_reset", "kgx_set_profile", "kgx_sync",
 ]
@@ -48,6 +48,8 @@ def lib():
         L.kgx_ingest_nvml.argtypes = [vp, vp, abi.u64p, abi.u64p]
         L.kgx_render_device.argtypes = [vp, C.POINTER(C.c_size_t)]
         L.kgx_render.argtypes = [vp, vp, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.kgx_render_begin.argtypes = [vp, vp, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.kgx_render_end.argtypes = [vp]
         L.kgx_body_device.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]
         L.kgx_body_offsets.argtypes = [vp, abi.u64p, C.c_size_t]
         L.kgx_read_values.argtypes = [vp, C.c_int, C.POINTER(C.c_double), abi.u32p, C.c_size_t, C.POINTER(C.c_size_t)]
@@ -156,6 +158,15 @@ class Kgx:
             return -int(n.value)
         self._chk(rc)
         return n.value
+
+    def render_begin(self, out):
+        """Render and start copying the body into `out` (pinned); returns the length.  Pair with render_end()."""
+        n = C.c_size_t()
+        self._chk(lib().kgx_render_begin(self._h, out.ctypes.data, out.nbytes, C.byref(n)))
+        return n.value
+
+    def render_end(self):
+        self._chk(lib().kgx_render_end(self._h))
 
     def render(self):
         if self._out is None:

@@ -268,3 +268,27 @@ def test_ingest_from_nvml_process_info_arrays(kgo):
     gx = kgx.Kgx(MODE_X)
     with pytest.raises(kgx.KgxError):
         gx.ingest_nvml(infos, dev_off, s.gpu_total)
+
+
+def test_pipelined_render_begin_end(kgo):
+    """kgx_render_begin/end: the body of scrape k is still being copied out while scrape k+1 is ingested."""
+    f = Fleet(n_nodes=6, pods=60, procs=500, seed=0xB200 + 8, scrapes=4)
+    t = f.table(MODE_X)
+    g, o = _pair(kgo, MODE_X, threads=2)
+    g.set_table(t); o.set_table(t)
+    bufs = [kgx.pinned_empty(8 << 20, np.uint8) for _ in range(2)]
+    want, got, lens = [], [], []
+    for k in range(4):
+        s = f.scrape(k)
+        g.reset_window(); o.reset_window()
+        g.ingest(s); o.ingest(s)            # overlaps the copy of body k-1
+        if k:
+            g.render_end()
+            got.append(bufs[(k - 1) % 2][:lens[-1]].tobytes())
+        lens.append(g.render_begin(bufs[k % 2]))
+        want.append(o.render())
+    g.render_end()
+    got.append(bufs[3 % 2][:lens[-1]].tobytes())
+    assert got == want
+    for b in bufs:
+        kgx.pinned_free(b)
