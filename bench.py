@@ -270,7 +270,7 @@ def main():
     alg_render = n_fam * label_bytes + body_len
     achieved = alg_render / (render_ms * 1e-3) / 1e9 if render_ms > 0 else 0.0
     alg_pipeline = cols.n * 36 + len(table.entry_pid) * 12 + alg_render
-    roofline = {"bound": "hbm", "kernel": "k_render3<64,false> (exposition writer)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": "k_render3<64> (exposition writer, kgx_writer.cuh)", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": ncu_traffic("r01_k_render3_raw.csv"), "peak_source": peak_src,
                 "traffic_source": "profiles/r01_k_render3_raw.csv (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, one launch)",
                 "algorithmic_bytes_per_launch": alg_render, "kernel_ms": render_ms,

@@ -12,8 +12,7 @@
 
 #include "../../include/kgx.h"
 #include "kgx_kernels.cuh"
-#include "kgx_render2.cuh"
-#include "kgx_render3.cuh"
+#include "kgx_writer.cuh"
 #include "kgx_ingest2.cuh"
 #include "kgx_table.hpp"
 
@@ -64,8 +63,6 @@ struct kgx_ctx {
   DBuf d_fam, d_tiles, d_tile_state, d_node_body_off, d_out;
   uint32_t n_tiles = 0, tile_lines = 0, render_smem = 0;
   bool render_v2 = false;  // second-generation writer (needs metric names of 15..64 bytes)
-  int render_kind = 1;         // 0 k_render2, 1 k_render3 direct stores, 2 k_render3 staged + TMA bulk store
-  bool render_direct = false;  // no output staging in shared memory (kind 1)
   RenderLayout lay{};
   int render_grid = 0, render_threads = 64;   // measured best on B200: direct stores, 64-line tiles
   size_t last_len = 0;
@@ -183,32 +180,22 @@ DevAcc acc_view(kgx_ctx* c) {
 }
 int n_acc_arrays(const kgx_ctx* c) { return c->mode == KGX_MODE_X ? 6 : 3; }
 
-// the writer is compiled for three CTA sizes (= lines per tile) and three data paths:
-// 0 k_render2 (late look-back, LSU flush), 1 k_render3 direct stores, 2 k_render3 staged + TMA bulk store
-#define KGX_RENDER_CASES(OP)                                                        \
-  switch (c->render_kind * 1000 + c->render_threads) {                              \
-    case 64: OP((k_render2<64>)); break;                                            \
-    case 128: OP((k_render2<128>)); break;                                          \
-    case 1032: OP((k_render3<32, false>)); break;                                   \
-    case 1064: OP((k_render3<64, false>)); break;                                   \
-    case 1128: OP((k_render3<128, false>)); break;                                  \
-    case 1256: OP((k_render3<256, false>)); break;                                  \
-    case 2064: OP((k_render3<64, true>)); break;                                    \
-    case 2128: OP((k_render3<128, true>)); break;                                   \
-    case 2256: OP((k_render3<256, true>)); break;                                   \
-    default: OP((k_render2<256>)); break;                                           \
+// the writer is compiled for four CTA sizes (= lines per tile); 64 measured best on B200
+const void* writer_func(const kgx_ctx* c) {
+  switch (c->render_threads) {
+    case 32: return reinterpret_cast<const void*>(&k_render3<32>);
+    case 128: return reinterpret_cast<const void*>(&k_render3<128>);
+    case 256: return reinterpret_cast<const void*>(&k_render3<256>);
+    default: return reinterpret_cast<const void*>(&k_render3<64>);
   }
-const void* render2_func(const kgx_ctx* c) {
-  const void* f = nullptr;
-#define KGX_OP(K) f = reinterpret_cast<const void*>(&K)
-  KGX_RENDER_CASES(KGX_OP)
-#undef KGX_OP
-  return f;
 }
-void launch_render2(kgx_ctx* c, int grid, const DevRender& R, unsigned long long* counters) {
-#define KGX_OP(K) K<<<grid, c->render_threads, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters)
-  KGX_RENDER_CASES(KGX_OP)
-#undef KGX_OP
+void launch_writer(kgx_ctx* c, int grid, const DevRender& R, unsigned long long* counters) {
+  switch (c->render_threads) {
+    case 32: k_render3<32><<<grid, 32, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+    case 128: k_render3<128><<<grid, 128, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+    case 256: k_render3<256><<<grid, 256, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+    default: k_render3<64><<<grid, 64, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+  }
 }
 
 DevLabels labels_view(kgx_ctx* c) {
@@ -420,27 +407,21 @@ int upload_plan(kgx_ctx* c) {
   c->render_v2 = min_name >= 15 && max_name <= 64 && c->fam.size() <= size_t(kMaxFamilies) && !getenv("KGX_RENDER_V1");
   int occ = 1;
   if (c->render_v2) {
-    // per line: value slot + staged label + output text; 3 CTAs per SM when labels are short
-    const uint64_t fixed = uint64_t(kMaxFamilies) * kNameStride + 64 + (64 + 16 + 128) + (max_header + 64);
-    if (const char* e = getenv("KGX_RENDER_KIND")) c->render_kind = atoi(e);
-    if (c->render_kind < 0 || c->render_kind > 2) c->render_kind = 1;
-    c->render_direct = c->render_kind == 1;
-    const uint64_t per_line = kSlotBytes + p.max_label_len + (c->render_direct ? 0 : max_line);
-    uint64_t budget = c->render_direct ? 35 * 1024 : 74 * 1024;
-    if (fixed + 16 * per_line > budget) budget = 200 * 1024;  // long labels: one CTA per SM
-    if (fixed + per_line > budget) return fail(c, KGX_E_LIMIT, "label text too long for one render tile");
+    // per line: value slot + staged label.  Small CTAs: many independent tiles per SM hide each other's latencies
     if (const char* e = getenv("KGX_RENDER_THREADS")) c->render_threads = atoi(e);
-    if (c->render_threads != 64 && c->render_threads != 128 && c->render_threads != 256 && !(c->render_threads == 32 && c->render_kind == 1)) c->render_threads = 64;
-    c->tile_lines = uint32_t(std::min<uint64_t>(uint64_t(c->render_threads), (budget - fixed) / per_line));
+    if (c->render_threads != 32 && c->render_threads != 128 && c->render_threads != 256) c->render_threads = 64;
+    const uint64_t fixed = uint64_t(kMaxFamilies) * kNameStride + uint64_t(c->render_threads) * kSlotBytes + 32 + (32 + 128 + 48) + 32;
+    uint64_t budget = 200 * 1024;
+    if (fixed + p.max_label_len > budget) return fail(c, KGX_E_LIMIT, "label text too long for one render tile");
+    c->tile_lines = uint32_t(std::min<uint64_t>(uint64_t(c->render_threads), (budget - fixed) / std::max<uint64_t>(1, p.max_label_len)));
     auto up16 = [](uint64_t v) { return uint32_t((v + 15) & ~15ull); };
     c->lay.names = 0;
     c->lay.slots = up16(uint64_t(kMaxFamilies) * kNameStride);
     c->lay.stage = up16(c->lay.slots + uint64_t(c->render_threads) * kSlotBytes + 32);
-    c->lay.out = up16(c->lay.stage + 32 + uint64_t(c->tile_lines) * p.max_label_len + 128 + 48);
-    c->lay.total = c->render_direct ? c->lay.out : up16(c->lay.out + 16 + max_header + uint64_t(c->tile_lines) * max_line + 48);
+    c->lay.total = up16(c->lay.stage + 32 + uint64_t(c->tile_lines) * p.max_label_len + 128 + 48);
     c->render_smem = c->lay.total;
-    KGX_CUDA(c, cudaFuncSetAttribute(render2_func(c), cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->render_smem)));
-    KGX_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, render2_func(c), c->render_threads, c->render_smem));
+    KGX_CUDA(c, cudaFuncSetAttribute(writer_func(c), cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->render_smem)));
+    KGX_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, writer_func(c), c->render_threads, c->render_smem));
   } else {
     const uint64_t budget = 96 * 1024;
     if (max_line + max_header + 32 > budget) return fail(c, KGX_E_LIMIT, "label text too long for one render tile");
@@ -540,11 +521,10 @@ int render_device_locked(kgx_ctx* c, size_t* len) {
   R.ser_gidx = ptr<uint32_t>(c->d_ser_gidx); R.gpu_total = ptr<unsigned long long>(c->d_gpu_total);
   R.tile_state = ptr<unsigned long long>(c->d_tile_state); R.node_body_off = ptr<unsigned long long>(c->d_node_body_off);
   R.out = ptr<uint8_t>(c->d_out); R.smem_bytes = c->render_smem;
-  R.flags = (getenv("KGX_RENDER_TMA_STORE") ? 1u : 0u) | (getenv("KGX_RENDER_LDGSTS") ? 2u : 0u);
   {
     Timed tm(c, KGX_K_RENDER);
     const int grid = int(std::min<uint32_t>(c->n_tiles, uint32_t(c->render_grid)));
-    if (c->render_v2) launch_render2(c, grid, R, ctr);
+    if (c->render_v2) launch_writer(c, grid, R, ctr);
     else k_render<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, acc_view(c), ctr);
     tm.launches(1);
     KGX_TRY(launch_check(c, "k_render"));
@@ -1024,7 +1004,7 @@ extern "C" int kgx_render_noalloc(kgx_ctx* c, uint8_t* d_out, size_t cap, size_t
   R.node_body_off = scratch + C_COUNT + kNoallocMaxTiles;
   R.out = d_out; R.smem_bytes = c->render_smem;
   const int grid = int(std::min<uint32_t>(c->n_tiles, uint32_t(c->render_grid)));
-  if (c->render_v2) launch_render2(c, grid, R, scratch);
+  if (c->render_v2) launch_writer(c, grid, R, scratch);
   else k_render<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, acc_view(c), scratch);
   c->stats.kernel_launches += 1;
   KGX_TRY(launch_check(c, "k_render (noalloc)"));

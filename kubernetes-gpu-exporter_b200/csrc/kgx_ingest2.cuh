@@ -14,7 +14,7 @@
 // memory by the same kernel (still node by node, for the L2 locality).
 #pragma once
 #include "kgx_kernels.cuh"
-#include "kgx_render2.cuh"  // mbarrier / bulk-copy helpers
+#include "kgx_async.cuh"
 
 namespace kgx {
 

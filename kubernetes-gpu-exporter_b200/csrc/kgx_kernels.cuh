@@ -339,7 +339,6 @@ struct DevRender {
   unsigned long long* node_body_off;    // [n_nodes+1]
   uint8_t* out;
   uint32_t smem_bytes;                  // capacity of the tile buffer
-  uint32_t flags;                       // bit0: tile body leaves through a TMA bulk store instead of the LSU
 };
 
 constexpr unsigned long long kStAgg = 1ull << 62, kStPrefix = 2ull << 62, kStMask = 3ull << 62;

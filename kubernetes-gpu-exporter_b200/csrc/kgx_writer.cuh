@@ -1,47 +1,85 @@
-// kgx_render3.cuh — exposition writer, direct-store variant (sm_100a).
+// kgx_writer.cuh — the exposition writer (sm_100a): series state + label text in,
+// Prometheus text exposition out, byte-identical to what the reference serves
+// through promhttp (main.go:69-71 -> Registry.Gather + expfmt, rules O1-O3, G1-G2,
+// F1-F5 of SURVEY.md 8c).  One pass, fused per tile of <= THREADS series of one
+// family of one node (exact lengths -> scan -> scatter, the north star's three
+// stages, without an intermediate):
 //
-// Same contract and same per-line streaming as k_render2 (kgx_render2.cuh), but
-// the tile text is never staged in shared memory: once the tile's global byte
-// offset is known, every lane stores its 16-byte chunks — aligned to the global
-// address — straight to the output with streaming STG.128.  Two lanes never
-// touch the same chunk (a chunk belongs to the line that holds its first byte),
-// so the only partial chunks of a tile are the head of its first line and the
-// tail of its last one; those few bytes go out as byte stores.
-// What it buys: no output buffer (about 60 % of k_render2's shared memory, so
-// twice the resident warps), no flush pass, one barrier fewer per tile.
-// What it costs: 16-byte stores that do not coalesce across lanes.
+//   * the label text of a tile is ONE contiguous byte range of the series label
+//     blob: a single TMA bulk copy (cp.async.bulk global->shared, completion on
+//     an mbarrier) stages it.  Warp 0 issues it for the NEXT tile — together
+//     with that tile's ticket and descriptor — before the CTA starts on it, so
+//     the ticket, the descriptor and the labels are not waited for;
+//   * each thread owns one line and formats its value once, straight into a
+//     shared-memory slot (" <value>\n");
+//   * line lengths -> CTA scan; the tile's size is published at once, and every
+//     warp resolves the tile's global byte offset itself by decoupled look-back
+//     over 32 predecessors per step.  Tickets are handed out in output order,
+//     so a tile never waits on one that has not started;
+//   * each thread then streams its line to the output as 16-byte chunks aligned
+//     to the GLOBAL address: a chunk belongs to the line that holds its first
+//     byte, so no two lanes ever write the same chunk and every store is a full
+//     streaming STG.128.  The four sources of a line (metric name, staged
+//     labels, value slot, head of the next line's name) are appended one after
+//     the other, all lanes of a warp in the same source at the same time; word
+//     loads + funnel shifts realign, computed byte masks merge the one chunk
+//     that straddles two sources.  Only the head of a tile's first line and the
+//     tail of its last one are partial chunks: those few bytes are byte stores.
+//
+// Needs metric names of 15..64 bytes (the tail of a chunk is completed with
+// the next line's name); other schemas take the generic k_render.
 #pragma once
-#include "kgx_render2.cuh"
+#include "kgx_async.cuh"
+#include "kgx_kernels.cuh"
 
 namespace kgx {
 
+struct RenderLayout {  // byte offsets inside dynamic shared memory (all 16-aligned)
+  uint32_t names;      // kMaxFamilies x 96: [16 pad][name (<=64)][16 pad]
+  uint32_t slots;      // THREADS x 28: " <value>\n"
+  uint32_t stage;      // staged label text (+32 slack before, +128+48 after)
+  uint32_t total;
+};
+constexpr uint32_t kSlotBytes = 28;  // 7 words: odd word stride -> conflict-free byte stores
+constexpr uint32_t kNameStride = 96;
+
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
 __device__ __forceinline__ void stg128_cs(uint8_t* p, uint4 v) {
   asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
+// bytes [0,e) from lo, bytes [e,16) from hi (0 < e < 16).  The masks are computed:
+// the writer is bound by the L1/LSU data pipe, not by the ALU.
+__device__ __forceinline__ uint4 merge16(uint4 lo, uint4 hi, uint32_t e) {
+  auto mk = [e](int w) -> uint32_t {  // the bytes of word w that are < e
+    const int n = min(max(int(e) - 4 * w, 0), 4);
+    return __funnelshift_rc(0xffffffffu, 0u, uint32_t(32 - 8 * n));
+  };
+  const uint4 m = make_uint4(mk(0), mk(1), mk(2), mk(3));
+  return make_uint4((lo.x & m.x) | (hi.x & ~m.x), (lo.y & m.y) | (hi.y & ~m.y), (lo.z & m.z) | (hi.z & ~m.z),
+                    (lo.w & m.w) | (hi.w & ~m.w));
+}
 
-template <int THREADS, bool STAGE>
+template <int THREADS>
 __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout lay, DevAcc acc, unsigned long long* counters) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ unsigned long long s_scan[THREADS / 32];
   __shared__ uint4 s_tail;
   __shared__ __align__(8) unsigned long long s_bar;
-  __shared__ __align__(16) uint32_t s_mask[16][4];
-  __shared__ uint32_t s_next;
-  __shared__ Tile s_desc;
-  __shared__ uint32_t s_l0;  // where the tile's first label starts inside the staged range
+  __shared__ uint32_t s_next;  // ticket of the tile to process next
+  __shared__ Tile s_desc;      // its descriptor
+  __shared__ uint32_t s_l0;    // where its first label starts inside the staged range
   const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const uint32_t sm0 = uint32_t(__cvta_generic_to_shared(smem));
   const uint32_t bar = uint32_t(__cvta_generic_to_shared(&s_bar));
+  // one-time: metric names of every family, with slack on both sides
   for (uint32_t i = tid; i < kMaxFamilies * kNameStride; i += THREADS) {
     const uint32_t f = i / kNameStride, o = i % kNameStride;
     smem[lay.names + i] = (o >= 16 && o < 16 + 64 && f < R.n_families) ? R.fam[f].name[o - 16] : uint8_t('#');
   }
-  for (uint32_t i = tid; i < 64; i += THREADS) {
-    const uint32_t e = i >> 2, w = i & 3;
-    const int n = int(e) - int(4 * w);
-    s_mask[e][w] = n <= 0 ? 0u : (n >= 4 ? 0xffffffffu : ((1u << (8 * n)) - 1u));
-  }
-  const uint32_t mask_sm = uint32_t(__cvta_generic_to_shared(&s_mask[0][0]));
   if (tid == 0) {
     mbar_init(bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -55,13 +93,13 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
     if (nt < R.n_tiles && lane == 0) {
       const Tile d = R.tiles[nt];
       const unsigned long long L0 = R.lbl_off[d.first], L1 = R.lbl_off[d.first + d.count];
-      const unsigned long long g0 = L0 & ~127ull;
+      const unsigned long long g0 = L0 & ~127ull;  // whole 128-byte lines
       const uint32_t bytes = uint32_t(((L1 + 15ull) & ~15ull) - g0);
       if (bytes) {
         mbar_expect_tx(bar, bytes);
         bulk_g2s(sm0 + lay.stage + 32, R.lbl_blob + g0, bytes, bar);
       } else {
-        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+        mbar_arrive(bar);
       }
       s_desc = d;
       s_l0 = uint32_t(L0 - g0);
@@ -74,10 +112,7 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
   uint32_t parity = 0;
   for (;;) {
     const uint32_t t = s_next;
-    if (t >= R.n_tiles) {
-      if (STAGE && tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // my bulk stores have landed
-      return;
-    }
+    if (t >= R.n_tiles) return;
     const Tile tile = s_desc;
     const uint32_t l0 = s_l0;
     const FamMeta& fm = R.fam[tile.family];
@@ -105,8 +140,7 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
     unsigned long long inc = mine;
     for (int o = 1; o < 32; o <<= 1) { unsigned long long u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
     if (lane == 31) s_scan[wid] = inc;
-    if (STAGE && tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // last tile's bulk store has read the tile buffer
-    __syncthreads();  // (1) also: everyone has read s_next / s_desc / s_g0
+    __syncthreads();  // (1) also: everyone has read s_next / s_desc / s_l0
     unsigned long long woff = 0, all = 0;
     for (int k = 0; k < THREADS / 32; ++k) { if (k < int(wid)) woff += s_scan[k]; all += s_scan[k]; }
     const unsigned long long exc = woff + inc - mine;
@@ -140,24 +174,24 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
       if (tile.flags & 2) R.node_body_off[tile.node] = base;
       if (t == R.n_tiles - 1) counters[C_TOTAL_LEN] = base + total;
     }
-    uint8_t* gtile = R.out + base;                    // first byte of the tile in the output
-    uint8_t* galn = R.out + (base & ~15ull);          // 16-aligned origin: position v lives at galn + v
+    uint8_t* gtile = R.out + base;            // first byte of the tile in the output
+    uint8_t* galn = R.out + (base & ~15ull);  // 16-aligned origin: position v lives at galn + v
     const uint32_t sh = uint32_t(base & 15);
-    const uint32_t outb = sm0 + lay.out;  // STAGE: position v lives at outb + v in shared memory
-    if (!STAGE && hdr) for (uint32_t i = tid; i < hdr; i += THREADS) gtile[i] = fm.header[i];
+    if (hdr) for (uint32_t i = tid; i < hdr; i += THREADS) gtile[i] = fm.header[i];
     mbar_wait(bar, parity);  // staged labels have landed (issued a whole tile ago)
     parity ^= 1;
     // ---- pass 2: stream my line to the output as 16-byte chunks aligned to the global address
     if (live) {
       const uint32_t g = sh + off;                                              // first byte of my line (position)
       const uint32_t b0 = g + name_len, b1 = b0 + lbl_len, b2 = b1 + vlen + 2;  // source boundaries; b2 = line end
-      const uint32_t start = (STAGE && first_live) ? (g & ~15u) : ((g + 15u) & ~15u);
-      const uint32_t stop = (!STAGE && last_live) ? (b2 & ~15u) : ((b2 + 15u) & ~15u);  // my chunks: [start, stop)
+      const uint32_t start = (g + 15u) & ~15u;
+      const uint32_t stop = last_live ? (b2 & ~15u) : ((b2 + 15u) & ~15u);      // my full chunks: [start, stop)
       const uint32_t name_sm = sm0 + lay.names + tile.family * kNameStride + 16;
       const uint32_t d0 = name_sm - g, d1 = lbl_src - b0, d2 = slot - b1, d3 = name_sm - b2;  // source = position + delta
-      if (!STAGE && first_live) {  // the bytes before my first aligned chunk: nobody else writes them
+      if (first_live) {  // the bytes before my first aligned chunk: nobody else writes them
         for (uint32_t q = g; q < start && q < b2; ++q) galn[q] = smem[lay.names + tile.family * kNameStride + 16 + (q - g)];
       }
+      // `a4` holds the chunk at p, of which the first `e` bytes are already final.
       uint32_t p = start, e = 0;
       uint4 a4 = make_uint4(0, 0, 0, 0);
       auto append = [&](uint32_t d, uint32_t b) {  // source = position + d, up to position b (exclusive)
@@ -171,14 +205,13 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
         };
         auto step = [&]() { wa += 16; w0 = w4; w1 = lds32(wa + 4); w2 = lds32(wa + 8); w3 = lds32(wa + 12); w4 = lds32(wa + 16); };
         const uint4 nw = chunk();
-        a4 = e ? merge16(a4, nw, e, mask_sm) : nw;
+        a4 = e ? merge16(a4, nw, e) : nw;
         if (b >= p + 16) {
-          if (STAGE) sts128(outb + p, a4); else stg128_cs(galn + p, a4);
+          stg128_cs(galn + p, a4);
           p += 16;
           step();
           while (p + 16 <= b) {
-            const uint4 c4 = chunk();
-            if (STAGE) sts128(outb + p, c4); else stg128_cs(galn + p, c4);
+            stg128_cs(galn + p, chunk());
             p += 16;
             step();
           }
@@ -189,34 +222,17 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
       append(d0, b0);  // metric name
       append(d1, b1);  // labels
       append(d2, b2);  // " <value>\n"
-      if (STAGE || !last_live) {
+      if (!last_live) {
         append(d3, stop);  // the head of the next line's name completes my last chunk
       } else if (e) {      // the tile ends inside a chunk: its bytes belong to me, the rest to the next tile
-        s_tail = a4;  // one thread per tile gets here: park the chunk, then byte-copy
+        s_tail = a4;       // one thread per tile gets here: park the chunk, then byte-copy
         const uint8_t* sp = reinterpret_cast<const uint8_t*>(&s_tail);
         for (uint32_t q = 0; q < e; ++q) galn[p + q] = sp[q];
       }
     }
-    __syncthreads();  // (2) label stage and value slots are free
-    if (STAGE) {
-      if (hdr) for (uint32_t i = tid; i < hdr; i += THREADS) smem[lay.out + sh + i] = fm.header[i];
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // my writes to the tile buffer -> visible to the bulk store
-    }
+    __syncthreads();             // (2) label stage and value slots are free
     if (wid == 0) fetch_next();  // next ticket, descriptor, label copy
-    __syncthreads();  // (3) s_next / s_desc / s_g0 visible
-    if (STAGE) {  // the tile leaves: byte head, one TMA bulk store for the 16-byte aligned body, byte tail
-      const uint32_t head = min(total, (16u - sh) & 15u);
-      const uint32_t body = (total - head) & ~15u;
-      if (tid == 0 && body) {
-        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gtile + head), "r"(outb + sh + head), "r"(body) : "memory");
-        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-      }
-      if (tid >= 32 && tid < 32 + head) gtile[tid - 32] = smem[lay.out + sh + tid - 32];
-      if (tid >= 48 && tid < 48 + (total - head - body)) {
-        const uint32_t i = head + body + tid - 48;
-        gtile[i] = smem[lay.out + sh + i];
-      }
-    }
+    __syncthreads();             // (3) s_next / s_desc / s_l0 visible
   }
 }
 
