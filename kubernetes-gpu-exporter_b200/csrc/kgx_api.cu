@@ -504,7 +504,9 @@ int ingest_device_locked(kgx_ctx* c, const kgx_cols* s) {
 
 int render_device_locked(kgx_ctx* c, size_t* len) {
   wait_copy(c);
-  if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_render before kgx_set_table");
+  // a scrape may arrive before the first poll cycle (the reference starts its HTTP server first, main.go:68-74):
+  // an empty registry gathers nothing, so the body is empty
+  if (!c->have_table) { c->last_len = 0; c->rendered = true; if (len) *len = 0; return KGX_OK; }
   if (c->n_tiles == 0) { c->last_len = 0; c->rendered = true; if (len) *len = 0; c->stats.rendered_bytes = 0; return KGX_OK; }
   unsigned long long* ctr = ptr<unsigned long long>(c->d_counters);
   {
@@ -807,7 +809,7 @@ int kgx_read_values(kgx_ctx* c, int family, double* values, uint32_t* slots, siz
   if (!c || !n_out) return KGX_E_INVAL;
   std::lock_guard<std::mutex> g(c->mu);
   cudaSetDevice(c->device);
-  if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_read_values before kgx_set_table");
+  if (!c->have_table) { *n_out = 0; return KGX_OK; }  // nothing registered yet: nothing to collect
   if (family < 0 || family >= int(c->fam.size())) return fail(c, KGX_E_INVAL, "family index out of range");
   const uint32_t S = c->n_series;
   *n_out = 0;

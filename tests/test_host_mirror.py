@@ -1,0 +1,31 @@
+"""The C++ host mirror of the reference interface (Exporter::Cycle, Describe /
+Collect, ServeHTTP) compiles against the C ABI; on a GPU box it is run against
+the golden body."""
+import os
+import subprocess
+
+import pytest
+
+from kgx_b200 import build
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SRC = os.path.join(ROOT, "tests", "host_mirror_test.cpp")
+
+
+def _compile(tmp_path):
+    so = build.build()
+    exe = str(tmp_path / "host_mirror_test")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-Wextra", SRC, "-o", exe, "-L" + os.path.dirname(so), "-lkgx",
+                           "-Wl,-rpath," + os.path.dirname(so), "-L/usr/local/cuda/lib64", "-Wl,-rpath,/usr/local/cuda/lib64"])
+    return exe
+
+
+def test_host_mirror_compiles_and_links(tmp_path):
+    assert os.path.exists(_compile(tmp_path))
+
+
+@pytest.mark.gpu
+def test_host_mirror_serves_the_golden_body(tmp_path):
+    exe = _compile(tmp_path)
+    r = subprocess.run([exe, os.path.join(ROOT, "tests", "golden", "r_single.txt")], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and r.stdout.strip() == "ok", r.stdout + r.stderr
