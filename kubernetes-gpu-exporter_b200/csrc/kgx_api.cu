@@ -647,6 +647,12 @@ int kgx_ingest(kgx_ctx* c, const kgx_cols* cols) {
   if (!cols->gpu_total) return fail(c, KGX_E_INVAL, "cols: gpu_total missing");
   kgx_cols d = *cols;
   const size_t n = size_t(cols->n);
+  if (cols->node_off) {  // the grouping promise is checked here, where the offsets are still host memory
+    const uint32_t NN = c->plan.n_nodes;
+    if (cols->node_off[0] != 0 || cols->node_off[NN] != n) return fail(c, KGX_E_INVAL, "cols: node_off must start at 0 and end at n");
+    for (uint32_t k = 0; k < NN; ++k)
+      if (cols->node_off[k + 1] < cols->node_off[k]) return fail(c, KGX_E_INVAL, "cols: node_off not ascending");
+  }
   const void* src[8] = {cols->pid, cols->gpu, cols->used, cols->node, cols->sm_util, cols->mem_util, cols->ts_us, cols->node_off};
   const size_t bytes[8] = {n * 4, n * 4, n * 8, n * 4, n * 4, n * 4, n * 8, (size_t(c->plan.n_nodes) + 1) * 8};
   const void* dst[8];
