@@ -39,18 +39,23 @@ def gather_bodies(local, dst=0, out=None, group=None):
     given on dst, is a preallocated uint8 tensor of at least the total size."""
     rank, world = dist.get_rank(group), dist.get_world_size(group)
     lengths, offsets = gather_layout(local.numel(), device=local.device, group=group)
+    # one batched group of point-to-point transfers: on NCCL they run concurrently over NVLink
+    # (unbatched send/recv would be serialised one peer after the other)
+    ops = []
     if rank == dst:
         total = int(offsets[-1])
         if out is None:
             out = torch.empty(total, dtype=torch.uint8, device=local.device)
         out[int(offsets[rank]):int(offsets[rank + 1])].copy_(local)
-        reqs = [dist.irecv(out[int(offsets[r]):int(offsets[r + 1])], src=r, group=group)
-                for r in range(world) if r != dst and lengths[r] > 0]
-        for q in reqs:
+        ops = [dist.P2POp(dist.irecv, out[int(offsets[r]):int(offsets[r + 1])], r, group)
+               for r in range(world) if r != dst and lengths[r] > 0]
+    elif local.numel() > 0:
+        ops = [dist.P2POp(dist.isend, local, dst, group)]
+    if ops:
+        for q in dist.batch_isend_irecv(ops):
             q.wait()
-        return out[:total], offsets
-    if local.numel() > 0:
-        dist.send(local, dst=dst, group=group)
+    if rank == dst:
+        return out[:int(offsets[-1])], offsets
     return None, offsets
 
 
