@@ -71,10 +71,22 @@ __global__ void __launch_bounds__(kIngestThreads) k_ingest_nodes(DevTable t, Dev
       __syncthreads();
     }
     bool marked_live = false;
+    // the columns of my next row are fetched while the current one is probed and folded
+    struct Row { uint32_t pid, gpu, sm, mem; unsigned long long used, ts; };
+    auto load_row = [&](unsigned long long i) {
+      Row w{};
+      w.pid = c.pid[i]; w.gpu = c.gpu[i];
+      if (XMODE) { w.used = c.used[i]; w.ts = c.ts_us[i]; w.sm = c.sm_util[i]; w.mem = c.mem_util[i]; }
+      return w;
+    };
+    Row nxt{};
+    if (lo + tid < hi) nxt = load_row(lo + tid);
     for (unsigned long long i = lo + tid; i < hi; i += kIngestThreads) {
-      const uint32_t gpu = c.gpu[i];
+      const Row row = nxt;
+      if (i + kIngestThreads < hi) nxt = load_row(i + kIngestThreads);
+      const uint32_t gpu = row.gpu;
       if (gpu >= t.G) { ++dropped; continue; }
-      const uint32_t pid = c.pid[i];
+      const uint32_t pid = row.pid;
       uint32_t pos = uint32_t((uint64_t(dev_hash_pid(pid)) * nt.cap) >> 32);
       bool hit = false;
       for (;;) {
@@ -102,14 +114,13 @@ __global__ void __launch_bounds__(kIngestThreads) k_ingest_nodes(DevTable t, Dev
           if (fold) {
             const uint32_t r = b.y + __popc(b.x & (bit - 1));
             if (XMODE) {
-              const unsigned long long used = c.used[i];
               atomicAdd(&acc.count[r], 1ull);
               if (!marked_live) { acc.node_live[node] = 1; marked_live = true; }  // only "non-zero" matters: plain store
-              atomicAdd(&acc.sum_used[r], used);
-              atomicMax(&acc.max_used[r], used);
-              atomicMax(&acc.last_ts[r], c.ts_us[i]);
-              atomicAdd(&acc.sum_sm[r], (unsigned long long)c.sm_util[i]);
-              atomicAdd(&acc.sum_mem[r], (unsigned long long)c.mem_util[i]);
+              atomicAdd(&acc.sum_used[r], row.used);
+              atomicMax(&acc.max_used[r], row.used);
+              atomicMax(&acc.last_ts[r], row.ts);
+              atomicAdd(&acc.sum_sm[r], (unsigned long long)row.sm);
+              atomicAdd(&acc.sum_mem[r], (unsigned long long)row.mem);
             } else {
               atomicMax(&acc.r_seq[r], (uint64_t(seq) << 32) | uint64_t(i));  // last write in sample order wins
             }
