@@ -57,6 +57,7 @@ struct kgx_ctx {
   std::vector<uint32_t> node_ser_off;
   // per-series state
   DBuf d_acc[6];  // X: sum_used,max_used,last_ts,sum_sm,sum_mem,count ; R: r_seq,r_used,r_total
+  DBuf d_acc_spare[6];  // target of the next index rebuild
   DBuf d_node_live, d_gpu_total;
   bool have_total = false;
   // render
@@ -104,7 +105,7 @@ int fail(kgx_ctx* c, int code, const char* msg) { c->err = msg; return code; }
 int dev_reserve(kgx_ctx* c, DBuf& b, size_t bytes) {
   if (bytes <= b.cap && b.p) return KGX_OK;
   if (b.p) { cudaFree(b.p); c->device_bytes -= b.cap; b.p = nullptr; b.cap = 0; }
-  size_t want = std::max<size_t>(bytes, 256);
+  size_t want = std::max<size_t>(bytes + bytes / 8, 256);  // headroom: series and tables grow a little every cycle
   KGX_CUDA(c, cudaMalloc(&b.p, want));
   b.cap = want;
   c->device_bytes += want;
@@ -243,7 +244,7 @@ int rebuild_index(kgx_ctx* c) {
   const uint32_t S = uint32_t(total);
   // new per-series state, zeroed, then the old state moved over
   const int na = n_acc_arrays(c);
-  DBuf new_acc[6];
+  DBuf* new_acc = c->d_acc_spare;  // the two sets swap roles at every rebuild: no allocation in steady churn
   for (int k = 0; k < na; ++k) {
     KGX_TRY(dev_reserve(c, new_acc[k], size_t(S) * 8));
     KGX_CUDA(c, cudaMemsetAsync(new_acc[k].p, 0, size_t(S) * 8, c->stream));
@@ -260,7 +261,7 @@ int rebuild_index(kgx_ctx* c) {
     tm.launches(1);
     KGX_CUDA(c, cudaStreamSynchronize(c->stream));  // h_old/h_new are stack arrays
   }
-  for (int k = 0; k < na; ++k) { dev_free(c, c->d_acc[k]); c->d_acc[k] = new_acc[k]; }
+  for (int k = 0; k < na; ++k) std::swap(c->d_acc[k], c->d_acc_spare[k]);
   // series arrays
   KGX_TRY(dev_reserve(c, c->d_ser_slot, size_t(S) * 4));
   KGX_TRY(dev_reserve(c, c->d_ser_a, size_t(S) * 4));
@@ -333,6 +334,15 @@ void free_table_state(kgx_ctx* c) {
                  &c->d_tiles, &c->d_tile_state, &c->d_node_body_off, &c->d_out};
   for (DBuf* b : all) dev_free(c, *b);
   for (auto& b : c->d_acc) dev_free(c, b);
+  for (auto& b : c->d_acc_spare) dev_free(c, b);
+  c->n_series = 0; c->n_tiles = 0; c->n_words = 0; c->lbl_bytes = 0; c->have_total = false; c->rendered = false;
+  c->last_len = 0;
+}
+
+// A new table replaces the old one in the same buffers (they only ever grow): under churn the
+// pod->PID map changes every cycle and must not cost thirty cudaFree/cudaMalloc pairs each time.
+void reset_table_state(kgx_ctx* c) {
+  wait_copy(c);
   c->n_series = 0; c->n_tiles = 0; c->n_words = 0; c->lbl_bytes = 0; c->have_total = false; c->rendered = false;
   c->last_len = 0;
 }
@@ -606,7 +616,7 @@ int kgx_set_table(kgx_ctx* c, const kgx_table* table) {
   std::string err;
   int rc = build_plan(c->mode, table, carried, &np, &err);
   if (rc != KGX_OK) { c->err = err; return rc; }
-  free_table_state(c);
+  reset_table_state(c);
   c->plan = std::move(np);
   c->have_table = true;
   KGX_TRY(upload_plan(c));
