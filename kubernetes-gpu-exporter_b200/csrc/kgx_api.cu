@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -610,16 +611,26 @@ int kgx_set_table(kgx_ctx* c, const kgx_table* table) {
   if (c->have_table && c->mode != KGX_MODE_X &&
       (table->n_nodes != c->plan.n_nodes || table->gpus_per_node != c->plan.G))
     return fail(c, KGX_E_INVAL, "R modes: n_nodes/gpus_per_node cannot change while series persist");
+  // KGX_TRACE=1: where the cold path spends its time (stderr)
+  const bool trace = getenv("KGX_TRACE") != nullptr;
+  auto now = [] { return std::chrono::steady_clock::now(); };
+  auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+    return std::chrono::duration<double, std::milli>(b - a).count();
+  };
+  const auto t0 = now();
   std::vector<Carried> carried;
   KGX_TRY(collect_carried(c, &carried));
+  const auto t1 = now();
   Plan np;
   std::string err;
   int rc = build_plan(c->mode, table, carried, &np, &err);
   if (rc != KGX_OK) { c->err = err; return rc; }
+  const auto t2 = now();
   reset_table_state(c);
   c->plan = std::move(np);
   c->have_table = true;
   KGX_TRY(upload_plan(c));
+  const auto t3 = now();
   c->stats.n_slots = c->plan.n_slots;
   if (!carried.empty()) {
     const uint32_t n = uint32_t(carried.size());
@@ -637,6 +648,9 @@ int kgx_set_table(kgx_ctx* c, const kgx_table* table) {
     KGX_TRY(launch_check(c, "carry-over"));
     KGX_CUDA(c, cudaStreamSynchronize(c->stream));
   }
+  if (trace)
+    fprintf(stderr, "kgx_set_table: read back %zu series %.2f ms, host plan %.2f ms, upload %.2f ms, re-seed %.2f ms\n",
+            carried.size(), ms(t0, t1), ms(t1, t2), ms(t2, t3), ms(t3, now()));
   return KGX_OK;
 }
 

@@ -138,7 +138,8 @@ int build_plan(int mode, const kgx_table* t, const std::vector<Carried>& carried
 
   // group podkeys and entries by node
   std::vector<std::vector<uint32_t>> node_pks(NN);
-  for (size_t i = 0; i < npk; ++i) node_pks[t->podkey_node[i]].push_back(uint32_t(i));
+  std::vector<uint32_t> pk_local(npk);  // position of a podkey among the podkeys of its node
+  for (size_t i = 0; i < npk; ++i) { pk_local[i] = uint32_t(node_pks[t->podkey_node[i]].size()); node_pks[t->podkey_node[i]].push_back(uint32_t(i)); }
   std::vector<uint32_t> pk_count(npk, 0);  // len(pids) of each podkey (R literal)
   std::vector<uint64_t> node_ent_off(NN + 1, 0);
   for (uint64_t e = 0; e < t->n_entries; ++e) { ++pk_count[t->entry_podkey[e]]; ++node_ent_off[t->podkey_node[t->entry_podkey[e]] + 1]; }
@@ -261,54 +262,53 @@ int build_plan(int mode, const kgx_table* t, const std::vector<Carried>& carried
       for (uint32_t r = 0; r < nord.size(); ++r) nrank[nord[r]] = r;
       const uint32_t pod_base = uint32_t(p.pod_names.size());
       for (auto nm : names) { p.pod_names.emplace_back(nm); p.pod_node.push_back(n); }
-      // pairs (pid label, local pod, joinable)
-      struct Pair { uint64_t pidkey; uint32_t prank, pid, pod; bool joinable; };
+      // pairs (pid label, pod): one packed 64-bit order key each = O3's (pid string, pod string) order.
+      // src: -1 = from the table (joinable), otherwise the index of the carried series it stands for.
+      struct Pair { uint64_t key; uint32_t pid, pod; int32_t src; };
+      if (names.size() >= (1u << 24)) return fail(KGX_E_LIMIT, "table: more than 2^24 pods on one node");
+      auto order_key = [&](uint32_t pid, uint32_t li) { return (decimal_string_key(pid) << 24) | nrank[li]; };
       std::vector<Pair> pairs;
       if (mode == KGX_MODE_R_LITERAL) {
         // main.go:144: `for pid := range pids` -> indices 0..len(pids)-1
         for (size_t li = 0; li < pks.size(); ++li)
-          for (uint32_t i = 0; i < pk_count[pks[li]]; ++i)
-            pairs.push_back(Pair{decimal_string_key(i), nrank[li], i, uint32_t(li), true});
+          for (uint32_t i = 0; i < pk_count[pks[li]]; ++i) pairs.push_back(Pair{order_key(i, uint32_t(li)), i, uint32_t(li), -1});
       } else {
+        pairs.reserve(size_t(node_ent_off[n + 1] - node_ent_off[n]) + node_carried[n].size());
         for (uint64_t k = node_ent_off[n]; k < node_ent_off[n + 1]; ++k) {
-          uint32_t e = ent_sorted[k];
-          uint32_t li = by_name[sv(t->pod_blob, t->pod_off, t->entry_podkey[e])];
-          pairs.push_back(Pair{decimal_string_key(t->entry_pid[e]), nrank[li], t->entry_pid[e], li, true});
+          const uint32_t e = ent_sorted[k];
+          const uint32_t li = pk_local[t->entry_podkey[e]];  // podkeys of a node are `names` in table order
+          pairs.push_back(Pair{order_key(t->entry_pid[e], li), t->entry_pid[e], li, -1});
         }
       }
       for (uint32_t ci : node_carried[n]) {
-        uint32_t li = by_name[std::string_view(carried[ci].pod)];
-        pairs.push_back(Pair{decimal_string_key(carried[ci].pid), nrank[li], carried[ci].pid, li, false});
+        const uint32_t li = by_name[std::string_view(carried[ci].pod)];
+        pairs.push_back(Pair{order_key(carried[ci].pid, li), carried[ci].pid, li, int32_t(ci)});
       }
-      // O3: (pid string, pod string); joinable copies first so unique keeps them
-      std::sort(pairs.begin(), pairs.end(), [](const Pair& a, const Pair& b) {
-        if (a.pidkey != b.pidkey) return a.pidkey < b.pidkey;
-        if (a.prank != b.prank) return a.prank < b.prank;
-        return a.joinable > b.joinable;
-      });
-      pairs.erase(std::unique(pairs.begin(), pairs.end(),
-                              [](const Pair& a, const Pair& b) { return a.pidkey == b.pidkey && a.prank == b.prank; }),
-                  pairs.end());
-      if (slot_total + pairs.size() >= 0x7ffffff0ull) return fail(KGX_E_LIMIT, "table: more than 2^31 potential series");
-      p.runs.push_back(Run{uint32_t(slot_total), uint32_t(pairs.size()), uint32_t(slot_total), 0xFFFFFFFFu, n});
-      std::unordered_map<uint64_t, uint32_t> slot_of;  // (pid, local pod) -> slot, for carried lookups
-      if (!node_carried[n].empty()) slot_of.reserve(pairs.size() * 2);
-      char num[16];
-      for (size_t i = 0; i < pairs.size(); ++i) {
-        const uint32_t slot = uint32_t(slot_total + i);
-        if (pairs[i].joinable) cells.emplace_back(pairs[i].pid, slot);
-        if (!node_carried[n].empty()) slot_of[(uint64_t(pairs[i].pid) << 32) | pairs[i].pod] = slot;
+      std::sort(pairs.begin(), pairs.end(), [](const Pair& a, const Pair& b) { return a.key != b.key ? a.key < b.key : a.src < b.src; });
+      // one slot per distinct key; a table copy (src -1) sorts first and makes the slot joinable
+      size_t n_new = 0;
+      p.A_blob.reserve(p.A_blob.size() + pairs.size() * 40);
+      for (size_t i = 0; i < pairs.size();) {
+        const uint32_t slot = uint32_t(slot_total + n_new);
+        if (pairs[i].src < 0) cells.emplace_back(pairs[i].pid, slot);
+        size_t j = i;
+        for (; j < pairs.size() && pairs[j].key == pairs[i].key; ++j)
+          if (pairs[j].src >= 0) p.carried_slot[size_t(pairs[j].src)] = slot;
         p.slot_pid.push_back(pairs[i].pid);
         p.slot_pod.push_back(pod_base + pairs[i].pod);
-        int nl = snprintf(num, sizeof num, "%u", pairs[i].pid);  // fmt.Sprintf("%d", pid), main.go:147
-        p.A_blob += "{pid=\""; p.A_blob.append(num, size_t(nl)); p.A_blob += "\",pod=\"";
+        char num[12];  // fmt.Sprintf("%d", pid), main.go:147
+        int nd = 0;
+        for (uint32_t v = pairs[i].pid; nd == 0 || v; v /= 10) num[11 - nd++] = char('0' + v % 10);
+        p.A_blob += "{pid=\""; p.A_blob.append(num + 12 - nd, size_t(nd)); p.A_blob += "\",pod=\"";
         append_escaped(p.A_blob, names[pairs[i].pod]); p.A_blob += "\"}";
         p.A_off.push_back(p.A_blob.size());
+        ++n_new;
+        i = j;
       }
-      for (uint32_t ci : node_carried[n])
-        p.carried_slot[ci] = slot_of[(uint64_t(carried[ci].pid) << 32) | by_name[std::string_view(carried[ci].pod)]];
-      slot_total += pairs.size();
-      p.n_a += pairs.size();
+      if (slot_total + n_new >= 0x7ffffff0ull) return fail(KGX_E_LIMIT, "table: more than 2^31 potential series");
+      p.runs.push_back(Run{uint32_t(slot_total), uint32_t(n_new), uint32_t(slot_total), 0xFFFFFFFFu, n});
+      slot_total += n_new;
+      p.n_a += n_new;
       std::sort(cells.begin(), cells.end());
     }
     p.node_tab[n] = NodeTab{uint32_t(tab_total), table_capacity(cells.size())};
