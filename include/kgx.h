@@ -219,7 +219,7 @@ int kgx_render(kgx_ctx* ctx, uint8_t* out, size_t cap, size_t* len);
  * array takes KGX_NOALLOC_SCRATCH_BYTES on every GPU that loads the library,
  * for the life of the process.  It makes no cudaMalloc/cudaFree (nor any other
  * allocating call) and leaves the ctx-owned body of kgx_render untouched.
- *   - Limits: at most KGX_NOALLOC_MAX_TILES render tiles (a tile is up to 256
+ *   - Limits: at most KGX_NOALLOC_MAX_TILES render tiles (a tile is up to 64
  *     series of one family of one node) and KGX_NOALLOC_MAX_NODES nodes;
  *     beyond that it returns KGX_E_LIMIT and kgx_render must be used.
  *   - `cap` must cover the worst-case body size; if it does not (or d_out is
@@ -229,9 +229,9 @@ int kgx_render(kgx_ctx* ctx, uint8_t* out, size_t cap, size_t* len);
  *   - All calls, from every ctx on that GPU, share the one array: it is cleared
  *     at the start of each call, and two calls that overlap on the GPU (two
  *     ctxs on different streams) race.  Serialise them. */
-#define KGX_NOALLOC_MAX_TILES 16384
+#define KGX_NOALLOC_MAX_TILES 65536
 #define KGX_NOALLOC_MAX_NODES 4096
-#define KGX_NOALLOC_SCRATCH_BYTES ((8 + KGX_NOALLOC_MAX_TILES + KGX_NOALLOC_MAX_NODES + 1) * 8) /* 163 912 */
+#define KGX_NOALLOC_SCRATCH_BYTES ((8 + KGX_NOALLOC_MAX_TILES + KGX_NOALLOC_MAX_NODES + 1) * 8) /* 557 128 */
 int kgx_render_noalloc(kgx_ctx* ctx, uint8_t* d_out, size_t cap, size_t* len);
 
 /* Split form of kgx_render for a pipelined exporter: kgx_render_begin renders,
