@@ -16,6 +16,7 @@
 #include "kgx_writer.cuh"
 #include "kgx_ingest2.cuh"
 #include "kgx_table.hpp"
+#include "kgx_build.cuh"
 
 using namespace kgx;
 
@@ -48,6 +49,15 @@ struct kgx_ctx {
   DBuf d_node_tab, d_tab, d_pk_slot0, d_pk_stride, d_grank, d_node_slot_base, d_node_a_base;
   uint32_t ingest_smem = 0, ingest_cells = 0, ingest_pks = 0, ingest_words = 0;  // staging buffer of the node-grouped join
   DBuf d_A_blob, d_B_blob, d_G_blob, d_A_off, d_B_off, d_G_off, d_runs;
+  uint32_t n_runs = 0;
+  // table build on the device (kgx_build.cuh): scratch chunks, and — R modes — who every slot and pod of the
+  // current generation is, so that series with a value can be carried into the next table without leaving the GPU
+  bool device_build = true, build_dirty = false;
+  std::vector<DBuf> arena;
+  size_t arena_i = 0, arena_off = 0;
+  DBuf d_slot_pid[2], d_slot_pod[2], d_pods_node[2], d_pods_blob[2], d_pods_off[2];
+  int gen = 0;
+  uint32_t n_pods = 0, max_words = 0;
   // index
   DBuf d_bm, d_pending, d_popc, d_prefix, d_block_sums;
   uint32_t n_words = 0;
@@ -205,7 +215,7 @@ DevLabels labels_view(kgx_ctx* c) {
   L.A_blob = ptr<uint8_t>(c->d_A_blob); L.B_blob = ptr<uint8_t>(c->d_B_blob); L.G_blob = ptr<uint8_t>(c->d_G_blob);
   L.A_off = ptr<unsigned long long>(c->d_A_off); L.B_off = ptr<unsigned long long>(c->d_B_off);
   L.G_off = ptr<unsigned long long>(c->d_G_off);
-  L.runs = ptr<Run>(c->d_runs); L.n_runs = uint32_t(c->plan.runs.size());
+  L.runs = ptr<Run>(c->d_runs); L.n_runs = c->n_runs;
   return L;
 }
 
@@ -336,6 +346,12 @@ void free_table_state(kgx_ctx* c) {
   for (DBuf* b : all) dev_free(c, *b);
   for (auto& b : c->d_acc) dev_free(c, b);
   for (auto& b : c->d_acc_spare) dev_free(c, b);
+  for (int g = 0; g < 2; ++g) {
+    dev_free(c, c->d_slot_pid[g]); dev_free(c, c->d_slot_pod[g]); dev_free(c, c->d_pods_node[g]);
+    dev_free(c, c->d_pods_blob[g]); dev_free(c, c->d_pods_off[g]);
+  }
+  for (auto& b : c->arena) dev_free(c, b);
+  c->arena.clear(); c->arena_i = 0; c->arena_off = 0; c->n_pods = 0; c->n_runs = 0;
   c->n_series = 0; c->n_tiles = 0; c->n_words = 0; c->lbl_bytes = 0; c->have_total = false; c->rendered = false;
   c->last_len = 0;
 }
@@ -376,19 +392,6 @@ int upload_plan(kgx_ctx* c) {
   KGX_TRY(upload(c, c->d_pk_stride, p.pk_stride.data(), p.pk_stride.size()));
   KGX_TRY(upload(c, c->d_grank, p.grank.data(), p.grank.size()));
   KGX_TRY(upload(c, c->d_node_a_base, p.node_a_base.data(), p.node_a_base.size()));
-  {  // node-grouped join: stage a node's table slice (+ its podkey slot tables) in shared memory when it fits
-    const uint64_t budget = 100 * 1024;  // two CTAs per SM
-    uint32_t max_words = 0;  // series-index words one node spans
-    for (uint32_t n = 0; n < p.n_nodes; ++n)
-      max_words = std::max(max_words, ((p.node_slot_base[n + 1] + 31) >> 5) - (p.node_slot_base[n] >> 5));
-    const uint64_t need = uint64_t(p.max_node_cells) * sizeof(Entry) + uint64_t(p.max_node_pks) * 8 + uint64_t(max_words) * 8;
-    if (need <= budget) { c->ingest_cells = p.max_node_cells; c->ingest_pks = p.max_node_pks; c->ingest_words = max_words; }
-    else { c->ingest_cells = 0; c->ingest_pks = 0; c->ingest_words = 0; }  // too large: probe in global memory, still node by node
-    c->ingest_smem = uint32_t(uint64_t(c->ingest_cells) * sizeof(Entry) + uint64_t(c->ingest_pks) * 8 + uint64_t(c->ingest_words) * 8 + 16);
-    const void* fns[] = {(const void*)&k_ingest_nodes<true, 0>, (const void*)&k_ingest_nodes<true, 1>,
-                         (const void*)&k_ingest_nodes<false, 0>, (const void*)&k_ingest_nodes<false, 1>};
-    for (const void* f : fns) KGX_CUDA(c, cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->ingest_smem)));
-  }
   KGX_TRY(upload(c, c->d_node_slot_base, p.node_slot_base.data(), p.node_slot_base.size()));
   KGX_TRY(upload(c, c->d_A_blob, p.A_blob.data(), p.A_blob.size()));
   KGX_TRY(upload(c, c->d_B_blob, p.B_blob.data(), p.B_blob.size()));
@@ -397,6 +400,28 @@ int upload_plan(kgx_ctx* c) {
   KGX_TRY(upload(c, c->d_B_off, p.B_off.data(), p.B_off.size()));
   KGX_TRY(upload(c, c->d_G_off, p.G_off.data(), p.G_off.size()));
   KGX_TRY(upload(c, c->d_runs, p.runs.data(), p.runs.size()));
+  c->n_runs = uint32_t(p.runs.size());
+  c->max_words = 0;  // series-index words one node spans
+  for (uint32_t n = 0; n < p.n_nodes; ++n)
+    c->max_words = std::max(c->max_words, ((p.node_slot_base[n + 1] + 31) >> 5) - (p.node_slot_base[n] >> 5));
+  return KGX_OK;
+}
+
+// Everything that depends on the table only through its sizes (plan.n_slots, n_nodes, G, max_*; ctx.max_words):
+// the join's staging buffer, the series index, the render tile geometry.  Shared by the host and the device build.
+int finish_plan(kgx_ctx* c) {
+  Plan& p = c->plan;
+  {  // node-grouped join: stage a node's table slice (+ its podkey slot tables) in shared memory when it fits
+    const uint64_t budget = 100 * 1024;  // two CTAs per SM
+    const uint32_t max_words = c->max_words;
+    const uint64_t need = uint64_t(p.max_node_cells) * sizeof(Entry) + uint64_t(p.max_node_pks) * 8 + uint64_t(max_words) * 8;
+    if (need <= budget) { c->ingest_cells = p.max_node_cells; c->ingest_pks = p.max_node_pks; c->ingest_words = max_words; }
+    else { c->ingest_cells = 0; c->ingest_pks = 0; c->ingest_words = 0; }  // too large: probe in global memory, still node by node
+    c->ingest_smem = uint32_t(uint64_t(c->ingest_cells) * sizeof(Entry) + uint64_t(c->ingest_pks) * 8 + uint64_t(c->ingest_words) * 8 + 16);
+    const void* fns[] = {(const void*)&k_ingest_nodes<true, 0>, (const void*)&k_ingest_nodes<true, 1>,
+                         (const void*)&k_ingest_nodes<false, 0>, (const void*)&k_ingest_nodes<false, 1>};
+    for (const void* f : fns) KGX_CUDA(c, cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->ingest_smem)));
+  }
   c->n_words = cdiv(p.n_slots, 32) + 1;
   KGX_TRY(dev_reserve(c, c->d_bm, size_t(c->n_words) * 8));
   KGX_TRY(dev_reserve(c, c->d_pending, size_t(c->n_words) * 4));
@@ -443,6 +468,49 @@ int upload_plan(kgx_ctx* c) {
   }
   c->render_grid = std::max(1, occ) * c->sm_count;
   KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  return KGX_OK;
+}
+
+}  // namespace
+#include "kgx_build_host.cuh"
+namespace {
+
+// kgx_set_table with the plan built on the GPU.  `*carried` receives what must be re-seeded after the index exists.
+int set_table_device(kgx_ctx* c, const kgx_table* t, CarriedDev* carried) {
+  const bool x = c->mode == KGX_MODE_X;
+  KGX_TRY(check_table_args(c, t, x));
+  wait_copy(c);
+  Arena ar(c);
+  c->build_dirty = false;
+  KGX_TAKE(uint32_t, small, 16);
+  KGX_CUDA(c, cudaMemsetAsync(small, 0, 64, c->stream));
+  const BuildSmall sm{small, small + 1, small + 1 + BS_COUNT};
+  TableIn in;
+  KGX_TRY(upload_table(c, ar, t, x, &in));
+  int rc;
+  if (x) {
+    rc = build_table_device_x(c, ar, in, sm);
+  } else {
+    const int g = c->gen;
+    const OldGen og{ptr<uint32_t>(c->d_slot_pid[g]), ptr<uint32_t>(c->d_slot_pod[g]), ptr<uint32_t>(c->d_pods_node[g]),
+                    ptr<uint8_t>(c->d_pods_blob[g]), ptr<unsigned long long>(c->d_pods_off[g]), c->have_table ? c->n_pods : 0u};
+    rc = collect_carried_device(c, ar, og, carried);
+    if (rc == KGX_OK) rc = build_table_device_r(c, ar, in, sm, og, *carried);
+  }
+  if (rc != KGX_OK) {
+    if (c->build_dirty) { c->have_table = false; reset_table_state(c); }  // the old table's buffers were already being rewritten
+    return rc;
+  }
+  uint32_t st[BS_COUNT] = {};
+  KGX_TRY(read_back(c, st, sm.stats, BS_COUNT));
+  Plan& p = c->plan;
+  const uint64_t n_slots = p.n_slots, n_a = p.n_a, n_entries = p.n_table_entries;
+  p = Plan();  // the host-side arrays of a host-built plan are stale now
+  p.mode = c->mode; p.n_nodes = t->n_nodes; p.G = t->gpus_per_node;
+  p.n_slots = n_slots; p.n_a = n_a; p.n_table_entries = n_entries;
+  p.max_label_len = st[BS_MAX_AB] + st[BS_MAX_G];
+  p.max_node_cells = st[BS_MAX_NODE_CELLS]; p.max_node_pks = st[BS_MAX_NODE_PKS];
+  c->max_words = st[BS_MAX_WORDS];
   return KGX_OK;
 }
 
@@ -575,6 +643,7 @@ int kgx_create(int device, const kgx_opts* opts, kgx_ctx** out) {
   kgx_ctx* c = new (std::nothrow) kgx_ctx();
   if (!c) return KGX_E_NOMEM;
   c->device = device; c->mode = opts->mode; c->profile = opts->profile != 0;
+  c->device_build = getenv("KGX_HOST_TABLE_BUILD") == nullptr;
   if (opts->stream) c->stream = static_cast<cudaStream_t>(opts->stream);
   else { if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return KGX_E_CUDA; } c->own_stream = true; }
   cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
@@ -618,6 +687,28 @@ int kgx_set_table(kgx_ctx* c, const kgx_table* table) {
     return std::chrono::duration<double, std::milli>(b - a).count();
   };
   const auto t0 = now();
+  if (c->device_build) {  // the plan is built on the GPU (kgx_build.cuh); KGX_HOST_TABLE_BUILD=1 at kgx_create selects the host builder
+    CarriedDev cd;
+    KGX_TRY(set_table_device(c, table, &cd));
+    const auto t1 = now();
+    reset_table_state(c);
+    c->have_table = true;
+    KGX_TRY(finish_plan(c));
+    c->stats.n_slots = c->plan.n_slots;
+    if (cd.n) {  // R modes: series that already had a value keep it (main.go never deletes a GaugeVec child)
+      k_set_bits<<<cdiv(cd.n, 256), 256, 0, c->stream>>>(cd.slot, cd.n, ptr<uint32_t>(c->d_pending));
+      KGX_TRY(rebuild_index(c));
+      k_seed_carried<<<cdiv(cd.n, 256), 256, 0, c->stream>>>(cd.slot, cd.used, cd.total, cd.n, ptr<uint2>(c->d_bm), acc_view(c));
+      c->stats.kernel_launches += 2;
+      KGX_CUDA(c, cudaMemsetAsync(c->d_pending.p, 0, size_t(c->n_words) * 4, c->stream));
+      KGX_TRY(launch_check(c, "carry-over"));
+      KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    if (trace)
+      fprintf(stderr, "kgx_set_table (device build): plan %.2f ms (%u carried series), index + re-seed %.2f ms\n", ms(t0, t1), cd.n,
+              ms(t1, now()));
+    return KGX_OK;
+  }
   std::vector<Carried> carried;
   KGX_TRY(collect_carried(c, &carried));
   const auto t1 = now();
@@ -630,6 +721,7 @@ int kgx_set_table(kgx_ctx* c, const kgx_table* table) {
   c->plan = std::move(np);
   c->have_table = true;
   KGX_TRY(upload_plan(c));
+  KGX_TRY(finish_plan(c));
   const auto t3 = now();
   c->stats.n_slots = c->plan.n_slots;
   if (!carried.empty()) {
@@ -873,6 +965,38 @@ int kgx_slot_labels(kgx_ctx* c, uint32_t slot, char* out, size_t cap, size_t* le
   if (!c || !len) return KGX_E_INVAL;
   std::lock_guard<std::mutex> g(c->mu);
   if (!c->have_table || slot >= c->plan.n_slots) return fail(c, KGX_E_INVAL, "slot out of range");
+  if (c->device_build) {  // the label pieces only exist on the GPU: fetch the three of this slot
+    cudaSetDevice(c->device);
+    if (c->plan.runs.size() != c->n_runs) {
+      c->plan.runs.resize(c->n_runs);
+      KGX_CUDA(c, cudaMemcpyAsync(c->plan.runs.data(), c->d_runs.p, size_t(c->n_runs) * sizeof(Run), cudaMemcpyDeviceToHost, c->stream));
+      KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    const std::vector<Run>& runs = c->plan.runs;
+    size_t lo = 0, hi = runs.size();
+    while (hi - lo > 1) { size_t mid = (lo + hi) / 2; if (runs[mid].slot_start <= slot) lo = mid; else hi = mid; }
+    const Run& r = runs[lo];
+    const uint32_t a = r.a_first + (slot - r.slot_start);
+    std::string s;
+    auto piece = [&](const DBuf& off, const DBuf& blob, uint64_t i) -> int {
+      unsigned long long o[2];
+      KGX_CUDA(c, cudaMemcpyAsync(o, ptr<unsigned long long>(off) + i, 16, cudaMemcpyDeviceToHost, c->stream));
+      KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+      const size_t at = s.size();
+      s.resize(at + size_t(o[1] - o[0]));
+      if (o[1] > o[0]) {
+        KGX_CUDA(c, cudaMemcpyAsync(&s[at], ptr<uint8_t>(blob) + o[0], size_t(o[1] - o[0]), cudaMemcpyDeviceToHost, c->stream));
+        KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+      }
+      return KGX_OK;
+    };
+    KGX_TRY(piece(c->d_A_off, c->d_A_blob, a));
+    if (r.gidx != 0xFFFFFFFFu) KGX_TRY(piece(c->d_G_off, c->d_G_blob, r.gidx));
+    KGX_TRY(piece(c->d_B_off, c->d_B_blob, a));
+    *len = s.size();
+    if (out && cap) memcpy(out, s.data(), std::min(cap, s.size()));
+    return KGX_OK;
+  }
   const Plan& p = c->plan;
   size_t lo = 0, hi = p.runs.size();
   while (hi - lo > 1) { size_t mid = (lo + hi) / 2; if (p.runs[mid].slot_start <= slot) lo = mid; else hi = mid; }
