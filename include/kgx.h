@@ -157,10 +157,14 @@ void kgx_destroy(kgx_ctx* ctx);
 
 /* ---- cold path ---------------------------------------------------------- */
 
-/* Install the join table (podPIDMap of main.go:84-114).  Builds, on the host,
- * the output order of every series the table can produce (Registry.Gather's
- * sort, see DESIGN.md "Order"), the pre-escaped label bytes and the
- * open-addressing hash table, and uploads them.
+/* Install the join table (podPIDMap of main.go:84-114).  Copies the caller's
+ * arrays to the GPU and builds there the output order of every series the
+ * table can produce (Registry.Gather's sort, see DESIGN.md "Order"), the
+ * pre-escaped label bytes and the open-addressing hash table.  (With
+ * KGX_HOST_TABLE_BUILD=1 in the environment at kgx_create the same plan is
+ * built by a host routine and uploaded; results are identical.)
+ * A table that is rejected (KGX_E_INVAL: ids out of range, label values that
+ * are not valid UTF-8, duplicate keys; KGX_E_LIMIT) leaves the ctx as it was.
  * R modes: series already exported keep their last value across calls, as
  * GaugeVec children do (main.go has no Delete/Reset).  X mode: clears the
  * window. */

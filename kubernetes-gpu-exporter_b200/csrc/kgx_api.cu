@@ -704,6 +704,15 @@ int kgx_set_table(kgx_ctx* c, const kgx_table* table) {
       KGX_TRY(launch_check(c, "carry-over"));
       KGX_CUDA(c, cudaStreamSynchronize(c->stream));
     }
+    {  // scratch of a small table is kept for the next cycle (churn); a fleet-sized one is given back
+      size_t held = 0;
+      for (const DBuf& b : c->arena) held += b.cap;
+      if (held > (size_t(256) << 20)) {
+        KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+        for (DBuf& b : c->arena) dev_free(c, b);
+        c->arena.clear();
+      }
+    }
     if (trace)
       fprintf(stderr, "kgx_set_table (device build): plan %.2f ms (%u carried series), index + re-seed %.2f ms\n", ms(t0, t1), cd.n,
               ms(t1, now()));

@@ -207,16 +207,18 @@ int build_table_device_x(kgx_ctx* c, Arena& ar, const TableIn& in, const BuildSm
   if (n_slots >= 0xfffffff0ull) return fail(c, KGX_E_LIMIT, "table: more than 2^32 potential series");
   if (2ull * n_cells + 8ull * NN >= 0xfffffff0ull) return fail(c, KGX_E_LIMIT, "table: hash table beyond 2^32 cells");
   KGX_TAKE(unsigned long long, lenA, npk + 1); KGX_TAKE(unsigned long long, lenB, npk + 1);
-  c->build_dirty = true;  // from here on the previous table's buffers are being overwritten
-  KGX_TRY(dev_reserve(c, c->d_pk_slot0, size_t(npk) * 4));
-  KGX_TRY(dev_reserve(c, c->d_pk_stride, size_t(npk) * 4));
+  KGX_TAKE(uint32_t, slot0_tmp, npk + 1); KGX_TAKE(uint32_t, stride_tmp, npk + 1);
   if (npk)
-    k_x_podkeys<<<cdiv(npk, B), B, 0, c->stream>>>(in, ord, run_id_incl, run_start, n_runs, run_slot, ptr<uint32_t>(c->d_pk_slot0),
-                                                   ptr<uint32_t>(c->d_pk_stride), lenA, lenB, sm.stats);
+    k_x_podkeys<<<cdiv(npk, B), B, 0, c->stream>>>(in, ord, run_id_incl, run_start, n_runs, run_slot, slot0_tmp, stride_tmp, lenA, lenB, sm.stats);
   uint32_t st[BS_COUNT] = {};
   KGX_TRY(read_back(c, st, sm.stats, BS_COUNT));
   if (uint64_t(st[BS_MAX_AB]) + st[BS_MAX_G] > 0x3fffffffull) return fail(c, KGX_E_LIMIT, "table: label text too long");
-  // ---------- phase 2: the rest of the ctx-owned buffers
+  // ---------- phase 2: the ctx-owned buffers
+  c->build_dirty = true;  // from here on the previous table's buffers are being overwritten
+  KGX_TRY(dev_reserve(c, c->d_pk_slot0, size_t(npk) * 4));
+  KGX_TRY(dev_reserve(c, c->d_pk_stride, size_t(npk) * 4));
+  KGX_CUDA(c, cudaMemcpyAsync(c->d_pk_slot0.p, slot0_tmp, size_t(npk) * 4, cudaMemcpyDeviceToDevice, c->stream));
+  KGX_CUDA(c, cudaMemcpyAsync(c->d_pk_stride.p, stride_tmp, size_t(npk) * 4, cudaMemcpyDeviceToDevice, c->stream));
   KGX_TRY(dev_reserve(c, c->d_A_off, (size_t(npk) + 1) * 8));
   KGX_TRY(dev_reserve(c, c->d_B_off, (size_t(npk) + 1) * 8));
   KGX_TRY(dev_reserve(c, c->d_G_off, (size_t(NG) + 1) * 8));
