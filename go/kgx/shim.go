@@ -138,6 +138,44 @@ func (c *Ctx) Ingest(s *Cols) error {
 	return c.err(C.kgx_ingest(c.p, &cc))
 }
 
+// IngestNvml feeds the R modes straight from go-nvml: infos is every device's
+// GetComputeRunningProcesses result concatenated in the loop order of main.go:123
+// (nvml.ProcessInfo has the C layout of nvmlProcessInfo_t), devOff the row range of
+// each device.  IngestNvmlX does the same for X mode with the utilisation samples
+// of nvml.Device.GetProcessUtilization beside them.
+func (c *Ctx) IngestNvml(infos []C.kgx_nvml_process_info, devOff, gpuTotal []uint64) error {
+	var pin runtime.Pinner
+	defer pin.Unpin()
+	var ip *C.kgx_nvml_process_info
+	if len(infos) > 0 {
+		pin.Pin(&infos[0])
+		ip = &infos[0]
+	}
+	pin.Pin(&devOff[0])
+	pin.Pin(&gpuTotal[0])
+	return c.err(C.kgx_ingest_nvml(c.p, ip, u64p(devOff), u64p(gpuTotal)))
+}
+
+func (c *Ctx) IngestNvmlX(infos []C.kgx_nvml_process_info, devOff []uint64, utils []C.kgx_nvml_process_utilization_sample,
+	utilOff, gpuTotal []uint64) error {
+	var pin runtime.Pinner
+	defer pin.Unpin()
+	var ip *C.kgx_nvml_process_info
+	var up *C.kgx_nvml_process_utilization_sample
+	if len(infos) > 0 {
+		pin.Pin(&infos[0])
+		ip = &infos[0]
+	}
+	if len(utils) > 0 {
+		pin.Pin(&utils[0])
+		up = &utils[0]
+	}
+	pin.Pin(&devOff[0])
+	pin.Pin(&utilOff[0])
+	pin.Pin(&gpuTotal[0])
+	return c.err(C.kgx_ingest_nvml_x(c.p, ip, u64p(devOff), up, u64p(utilOff), u64p(gpuTotal)))
+}
+
 func (c *Ctx) ResetWindow() error { return c.err(C.kgx_reset_window(c.p)) }
 
 // Render returns the text exposition; buf is reused when large enough.

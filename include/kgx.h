@@ -198,6 +198,28 @@ typedef struct kgx_nvml_process_info {  /* = nvmlProcessInfo_t, 24 bytes */
 int kgx_ingest_nvml(kgx_ctx* ctx, const kgx_nvml_process_info* infos, const uint64_t* dev_off,
                     const uint64_t* gpu_total);
 
+/* X mode: the same for the wider sample.  NVML reports a process twice: memory
+ * in nvmlProcessInfo_t (as above) and utilisation in
+ * nvmlProcessUtilizationSample_t (nvmlDeviceGetProcessUtilization; struct at
+ * nvml.h:1277-1285).  `utils` is every device's sample array concatenated in
+ * the same device order, util_off[node*G+gpu] .. util_off[node*G+gpu+1] the
+ * samples of one device.  A sample row is one process-info row joined, on the
+ * GPU, with the utilisation sample of the same pid on the same device (the last
+ * one in array order if a pid occurs twice; sm = mem = timestamp = 0 if none);
+ * utilisation samples without a process-info row are ignored.  The reference
+ * never calls this NVML function: X mode is the extension. */
+typedef struct kgx_nvml_process_utilization_sample {  /* = nvmlProcessUtilizationSample_t, 32 bytes */
+  uint32_t pid;
+  uint32_t pad_;
+  uint64_t time_stamp;  /* CPU timestamp in microseconds */
+  uint32_t sm_util;
+  uint32_t mem_util;
+  uint32_t enc_util;
+  uint32_t dec_util;
+} kgx_nvml_process_utilization_sample;
+int kgx_ingest_nvml_x(kgx_ctx* ctx, const kgx_nvml_process_info* infos, const uint64_t* dev_off,
+                      const kgx_nvml_process_utilization_sample* utils, const uint64_t* util_off, const uint64_t* gpu_total);
+
 /* X mode: start a new aggregation window (forget sums/max/last/count).
  * No-op error KGX_E_STATE in R modes, whose series never reset. */
 int kgx_reset_window(kgx_ctx* ctx);

@@ -15,6 +15,10 @@ K_NAMES = ["ingest", "finalize", "index", "render", "other"]
 NVML_PROCESS_INFO = np.dtype([("pid", "<u4"), ("pad_", "<u4"), ("used_gpu_memory", "<u8"),
                               ("gpu_instance_id", "<u4"), ("compute_instance_id", "<u4")])
 
+# nvmlProcessUtilizationSample_t (nvml.h:1277-1285): 32 bytes
+NVML_PROCESS_UTILIZATION_SAMPLE = np.dtype([("pid", "<u4"), ("pad_", "<u4"), ("time_stamp", "<u8"), ("sm_util", "<u4"),
+                                            ("mem_util", "<u4"), ("enc_util", "<u4"), ("dec_util", "<u4")])
+
 u32p = C.POINTER(C.c_uint32)
 u64p = C.POINTER(C.c_uint64)
 

@@ -84,7 +84,7 @@ struct kgx_ctx {
   DBuf d_counters;
   unsigned long long* h_counters = nullptr;  // pinned
   DBuf d_cols[8];
-  DBuf d_tmp[4];
+  DBuf d_tmp[6];
   uint32_t seq = 0;
   kgx_stats stats{};
   kgx_profile prof{};
@@ -829,6 +829,57 @@ int kgx_ingest_nvml(kgx_ctx* c, const kgx_nvml_process_info* infos, const uint64
   d.n = n;
   d.pid = ptr<uint32_t>(c->d_cols[0]); d.gpu = ptr<uint32_t>(c->d_cols[1]); d.used = ptr<uint64_t>(c->d_cols[2]);
   d.node = ptr<uint32_t>(c->d_cols[3]); d.node_off = ptr<uint64_t>(c->d_cols[7]); d.gpu_total = gpu_total;
+  return ingest_device_locked(c, &d);
+}
+
+int kgx_ingest_nvml_x(kgx_ctx* c, const kgx_nvml_process_info* infos, const uint64_t* dev_off,
+                      const kgx_nvml_process_utilization_sample* utils, const uint64_t* util_off, const uint64_t* gpu_total) {
+  if (!c) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  if (c->mode != KGX_MODE_X) return fail(c, KGX_E_STATE, "kgx_ingest_nvml_x: X mode only (R modes take kgx_ingest_nvml)");
+  if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_ingest_nvml_x before kgx_set_table");
+  if (!dev_off || !util_off || !gpu_total) return fail(c, KGX_E_INVAL, "kgx_ingest_nvml_x: dev_off / util_off / gpu_total missing");
+  static_assert(sizeof(kgx_nvml_process_utilization_sample) == 32 && sizeof(NvmlProcessUtilizationSample) == 32,
+                "nvmlProcessUtilizationSample_t is 32 bytes");
+  const uint32_t n_dev = c->plan.n_nodes * c->plan.G;
+  if (dev_off[0] != 0 || util_off[0] != 0) return fail(c, KGX_E_INVAL, "kgx_ingest_nvml_x: dev_off[0] and util_off[0] must be 0");
+  for (uint32_t d = 0; d < n_dev; ++d)
+    if (dev_off[d + 1] < dev_off[d] || util_off[d + 1] < util_off[d]) return fail(c, KGX_E_INVAL, "kgx_ingest_nvml_x: offsets not ascending");
+  const size_t n = size_t(dev_off[n_dev]), m = size_t(util_off[n_dev]);
+  if ((n && !infos) || (m && !utils)) return fail(c, KGX_E_INVAL, "kgx_ingest_nvml_x: infos / utils missing");
+  KGX_TRY(dev_reserve(c, c->d_tmp[1], n * 24));
+  KGX_TRY(dev_reserve(c, c->d_tmp[2], (size_t(n_dev) + 1) * 8));
+  KGX_TRY(dev_reserve(c, c->d_tmp[4], m * 32));
+  KGX_TRY(dev_reserve(c, c->d_tmp[5], (size_t(n_dev) + 1) * 8));
+  const size_t bytes[8] = {n * 4, n * 4, n * 8, n * 4, n * 4, n * 4, n * 8, (size_t(c->plan.n_nodes) + 1) * 8};
+  for (int k = 0; k < 8; ++k) KGX_TRY(dev_reserve(c, c->d_cols[k], bytes[k]));
+  if (n) KGX_CUDA(c, cudaMemcpyAsync(c->d_tmp[1].p, infos, n * 24, cudaMemcpyHostToDevice, c->stream));
+  if (m) KGX_CUDA(c, cudaMemcpyAsync(c->d_tmp[4].p, utils, m * 32, cudaMemcpyHostToDevice, c->stream));
+  KGX_CUDA(c, cudaMemcpyAsync(c->d_tmp[2].p, dev_off, (size_t(n_dev) + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+  KGX_CUDA(c, cudaMemcpyAsync(c->d_tmp[5].p, util_off, (size_t(n_dev) + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+  {
+    Timed tm(c, KGX_K_OTHER);
+    if (n) {
+      k_unpack_nvml<<<cdiv(n, 256), 256, 0, c->stream>>>(ptr<NvmlProcessInfo>(c->d_tmp[1]), ptr<unsigned long long>(c->d_tmp[2]), n_dev, c->plan.G,
+                                                         n, ptr<uint32_t>(c->d_cols[0]), ptr<uint32_t>(c->d_cols[1]), ptr<uint32_t>(c->d_cols[3]),
+                                                         ptr<unsigned long long>(c->d_cols[2]));
+      const int grid = int(std::min<uint32_t>(n_dev, uint32_t(c->sm_count) * 8));
+      k_join_nvml_util<<<grid, kUtilThreads, 0, c->stream>>>(ptr<unsigned long long>(c->d_tmp[2]), ptr<NvmlProcessUtilizationSample>(c->d_tmp[4]),
+                                                             ptr<unsigned long long>(c->d_tmp[5]), n_dev, ptr<uint32_t>(c->d_cols[0]),
+                                                             ptr<uint32_t>(c->d_cols[4]), ptr<uint32_t>(c->d_cols[5]),
+                                                             ptr<unsigned long long>(c->d_cols[6]));
+    }
+    k_node_off_from_dev_off<<<cdiv(c->plan.n_nodes + 1, 256), 256, 0, c->stream>>>(ptr<unsigned long long>(c->d_tmp[2]), c->plan.n_nodes,
+                                                                                  c->plan.G, ptr<unsigned long long>(c->d_cols[7]));
+    tm.launches(n ? 3 : 1);
+    KGX_TRY(launch_check(c, "k_join_nvml_util"));
+  }
+  kgx_cols d{};
+  d.n = n;
+  d.pid = ptr<uint32_t>(c->d_cols[0]); d.gpu = ptr<uint32_t>(c->d_cols[1]); d.used = ptr<uint64_t>(c->d_cols[2]);
+  d.node = ptr<uint32_t>(c->d_cols[3]); d.sm_util = ptr<uint32_t>(c->d_cols[4]); d.mem_util = ptr<uint32_t>(c->d_cols[5]);
+  d.ts_us = ptr<uint64_t>(c->d_cols[6]); d.node_off = ptr<uint64_t>(c->d_cols[7]); d.gpu_total = gpu_total;
   return ingest_device_locked(c, &d);
 }
 

@@ -475,6 +475,63 @@ __global__ void k_node_off_from_dev_off(const unsigned long long* dev_off, uint3
   if (n <= n_nodes) node_off[n] = dev_off[size_t(n) * G];
 }
 
+// X mode: a sample row = a process-info row + the utilisation sample NVML reports for the same pid on the same
+// device (nvmlDeviceGetProcessUtilization; the last one in array order when a pid occurs twice; none -> sm = mem =
+// ts = 0).  One CTA per device at a time: the device's samples go into a shared-memory hash, its rows probe it.
+struct NvmlProcessUtilizationSample { uint32_t pid, pad_; unsigned long long ts; uint32_t sm, mem, enc, dec; };  // nvml.h:1277-1285
+constexpr uint32_t kUtilCells = 2048;
+constexpr int kUtilThreads = 256;
+__global__ void __launch_bounds__(kUtilThreads) k_join_nvml_util(const unsigned long long* dev_off, const NvmlProcessUtilizationSample* utils,
+                                                                  const unsigned long long* util_off, uint32_t n_dev, const uint32_t* pid_col,
+                                                                  uint32_t* sm, uint32_t* mem, unsigned long long* ts) {
+  __shared__ unsigned long long cells[kUtilCells];  // pid << 32 | (index + 1); 0 = empty
+  const uint32_t tid = threadIdx.x;
+  for (uint32_t d = blockIdx.x; d < n_dev; d += gridDim.x) {
+    const unsigned long long r0 = dev_off[d], r1 = dev_off[d + 1], u0 = util_off[d], m = util_off[d + 1] - u0;
+    if (r1 == r0) continue;  // uniform over the CTA
+    const bool hashed = m * 2 <= kUtilCells;
+    if (hashed) {
+      for (uint32_t i = tid; i < kUtilCells; i += kUtilThreads) cells[i] = 0;
+      __syncthreads();
+      for (uint32_t j = tid; j < m; j += kUtilThreads) {
+        const uint32_t pid = utils[u0 + j].pid;
+        const unsigned long long mine = ((unsigned long long)pid << 32) | (j + 1);
+        uint32_t pos = dev_hash_pid(pid) & (kUtilCells - 1);
+        for (;;) {
+          const unsigned long long old = atomicCAS(&cells[pos], 0ull, mine);
+          if (old == 0) break;
+          if (uint32_t(old >> 32) == pid) { atomicMax(&cells[pos], mine); break; }
+          pos = (pos + 1) & (kUtilCells - 1);
+        }
+      }
+      __syncthreads();
+    }
+    for (unsigned long long i = r0 + tid; i < r1; i += kUtilThreads) {
+      const uint32_t pid = pid_col[i];
+      long long found = -1;
+      if (hashed) {
+        uint32_t pos = dev_hash_pid(pid) & (kUtilCells - 1);
+        for (;;) {
+          const unsigned long long cell = cells[pos];
+          if (cell == 0) break;
+          if (uint32_t(cell >> 32) == pid) { found = (long long)(cell & 0xffffffffull) - 1; break; }
+          pos = (pos + 1) & (kUtilCells - 1);
+        }
+      } else {  // an unusually crowded device: scan its samples
+        for (unsigned long long j = 0; j < m; ++j)
+          if (utils[u0 + j].pid == pid) found = (long long)j;
+      }
+      if (found >= 0) {
+        const NvmlProcessUtilizationSample u = utils[u0 + found];
+        sm[i] = u.sm; mem[i] = u.mem; ts[i] = u.ts;
+      } else {
+        sm[i] = 0; mem[i] = 0; ts[i] = 0;
+      }
+    }
+    __syncthreads();  // the hash is cleared for the next device
+  }
+}
+
 // ---- float printer entry (tests) ---------------------------------------------------------
 __global__ void k_format_values(const double* v, uint64_t n, uint8_t* out32) {
   const uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;

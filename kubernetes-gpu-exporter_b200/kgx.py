@@ -15,7 +15,7 @@ _LIB = None
 
 EXPORTS = [
     "kgx_abi_version", "kgx_strerror", "kgx_last_error", "kgx_create", "kgx_destroy", "kgx_set_table", "kgx_ingest",
-    "kgx_ingest_device", "kgx_ingest_nvml", "kgx_reset_window", "kgx_render_device", "kgx_render", "kgx_render_begin", "kgx_render_end", "kgx_body_device", "kgx_body_offsets",
+    "kgx_ingest_device", "kgx_ingest_nvml", "kgx_ingest_nvml_x", "kgx_reset_window", "kgx_render_device", "kgx_render", "kgx_render_begin", "kgx_render_end", "kgx_body_device", "kgx_body_offsets",
     "kgx_read_values", "kgx_family_count", "kgx_family_info", "kgx_slot_labels", "kgx_format_values", "kgx_host_alloc",
     "kgx_host_free", "kgx_get_stats", "kgx_get_profile", "kgx_profile_reset", "kgx_set_profile", "kgx_sync",
 ]
@@ -46,6 +46,7 @@ def lib():
         L.kgx_ingest_device.argtypes = [vp, C.POINTER(abi.kgx_cols)]
         L.kgx_reset_window.argtypes = [vp]
         L.kgx_ingest_nvml.argtypes = [vp, vp, abi.u64p, abi.u64p]
+        L.kgx_ingest_nvml_x.argtypes = [vp, vp, abi.u64p, vp, abi.u64p, abi.u64p]
         L.kgx_render_device.argtypes = [vp, C.POINTER(C.c_size_t)]
         L.kgx_render.argtypes = [vp, vp, C.c_size_t, C.POINTER(C.c_size_t)]
         L.kgx_render_begin.argtypes = [vp, vp, C.c_size_t, C.POINTER(C.c_size_t)]
@@ -141,6 +142,16 @@ class Kgx:
         gpu_total = np.ascontiguousarray(gpu_total, dtype=np.uint64)
         self._chk(lib().kgx_ingest_nvml(self._h, infos.ctypes.data, dev_off.ctypes.data_as(abi.u64p),
                                         gpu_total.ctypes.data_as(abi.u64p)))
+
+    def ingest_nvml_x(self, infos, dev_off, utils, util_off, gpu_total):
+        """X mode: nvmlProcessInfo_t rows joined on the GPU with nvmlProcessUtilizationSample_t rows (same pid, same device)."""
+        infos = np.ascontiguousarray(infos, dtype=abi.NVML_PROCESS_INFO)
+        utils = np.ascontiguousarray(utils, dtype=abi.NVML_PROCESS_UTILIZATION_SAMPLE)
+        dev_off = np.ascontiguousarray(dev_off, dtype=np.uint64)
+        util_off = np.ascontiguousarray(util_off, dtype=np.uint64)
+        gpu_total = np.ascontiguousarray(gpu_total, dtype=np.uint64)
+        self._chk(lib().kgx_ingest_nvml_x(self._h, infos.ctypes.data, dev_off.ctypes.data_as(abi.u64p), utils.ctypes.data,
+                                          util_off.ctypes.data_as(abi.u64p), gpu_total.ctypes.data_as(abi.u64p)))
 
     def reset_window(self):
         self._chk(lib().kgx_reset_window(self._h))

@@ -270,6 +270,67 @@ def test_ingest_from_nvml_process_info_arrays(kgo):
         gx.ingest_nvml(infos, dev_off, s.gpu_total)
 
 
+def test_x_ingest_from_nvml_info_and_utilization_arrays(kgo):
+    """X mode from the two NVML wire formats (nvmlProcessInfo_t + nvmlProcessUtilizationSample_t per device): the GPU
+    joins them by (device, pid); same body as the columns that join produces on the host."""
+    from kgx_b200 import abi
+    rng = np.random.default_rng(0xB200 + 77)
+    f = Fleet(n_nodes=7, pods=40, procs=900, seed=0xB200 + 3)  # ~16 processes per device; one device made crowded below
+    t = f.table(MODE_X)
+    s = f.scrape(0)
+    order = np.lexsort((np.arange(s.n), s.gpu, s.node))
+    pid, gpu, node, used = s.pid[order], s.gpu[order], s.node[order], s.used[order]
+    sm, mem, ts = s.sm_util[order].copy(), s.mem_util[order].copy(), s.ts_us[order].copy()
+    gpu[node == 3] = 2  # every process of node 3 on one device; with the filler below it exceeds the shared-memory hash
+    order2 = np.lexsort((np.arange(s.n), gpu, node))
+    pid, gpu, node, used, sm, mem, ts = (a[order2] for a in (pid, gpu, node, used, sm, mem, ts))
+    dev = node.astype(np.int64) * f.G + gpu
+    n_dev = f.n_nodes * f.G
+    dev_off = np.zeros(n_dev + 1, dtype=np.uint64)
+    dev_off[1:] = np.cumsum(np.bincount(dev, minlength=n_dev))
+    infos = np.zeros(s.n, dtype=abi.NVML_PROCESS_INFO)
+    infos["pid"], infos["used_gpu_memory"] = pid, used
+    # utilisation samples: per device, in another order; 10 % of the processes have none; some pids have two (last wins);
+    # some samples belong to no process
+    urows, want_sm, want_mem, want_ts = [], sm.copy(), mem.copy(), ts.copy()
+    util_off = np.zeros(n_dev + 1, dtype=np.uint64)
+    for d in range(n_dev):
+        lo, hi = int(dev_off[d]), int(dev_off[d + 1])
+        rows = []
+        last = {}
+        for i in rng.permutation(np.arange(lo, hi)):
+            if rng.random() < 0.1:
+                continue
+            if rng.random() < 0.15:
+                rows.append((pid[i], 1, 2, 3))       # an older sample of the same pid, superseded below
+            rows.append((pid[i], ts[i], sm[i], mem[i]))
+        for _ in range(3):
+            rows.append((4_000_000_000 - d, 9, 9, 9))  # a process NVML has utilisation for but no memory record
+        if d == 3 * f.G + 2:
+            rows += [(5_000_000 + k, 1, 1, 1) for k in range(1100)]  # crowded device
+        for j, r in enumerate(rows):
+            last[int(r[0])] = r
+        for i in range(lo, hi):
+            r = last.get(int(pid[i]))
+            want_ts[i], want_sm[i], want_mem[i] = (r[1], r[2], r[3]) if r else (0, 0, 0)
+        urows += rows
+        util_off[d + 1] = len(urows)
+    utils = np.zeros(len(urows), dtype=abi.NVML_PROCESS_UTILIZATION_SAMPLE)
+    utils["pid"] = [r[0] for r in urows]; utils["time_stamp"] = [r[1] for r in urows]
+    utils["sm_util"] = [r[2] for r in urows]; utils["mem_util"] = [r[3] for r in urows]
+    utils["enc_util"], utils["dec_util"] = 7, 8
+    g, o = _pair(kgo, MODE_X)
+    g.set_table(t); o.set_table(t)
+    for _ in range(2):
+        g.ingest_nvml_x(infos, dev_off, utils, util_off, s.gpu_total)
+        o.ingest(Cols(pid=pid, gpu=gpu, used=used, node=node, sm_util=want_sm, mem_util=want_mem, ts_us=want_ts, gpu_total=s.gpu_total))
+        assert len(_same(g, o)) > 0
+    gr = kgx.Kgx(MODE_R_INTENDED)
+    gr.set_table(f.table(MODE_R_INTENDED))
+    with pytest.raises(kgx.KgxError):
+        gr.ingest_nvml_x(infos, dev_off, utils, util_off, s.gpu_total)
+
+
 def test_pipelined_render_begin_end(kgo):
     """kgx_render_begin/end: the body of scrape k is still being copied out while scrape k+1 is ingested."""
     f = Fleet(n_nodes=6, pods=60, procs=500, seed=0xB200 + 8, scrapes=4)
