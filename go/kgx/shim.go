@@ -178,6 +178,15 @@ func (c *Ctx) IngestNvmlX(infos []C.kgx_nvml_process_info, devOff []uint64, util
 
 func (c *Ctx) ResetWindow() error { return c.err(C.kgx_reset_window(c.p)) }
 
+// Expire drops the X-mode series whose newest sample is older than the cutoff
+// (microseconds, the clock of Cols.TsUs) and returns how many exported series
+// went.  R modes refuse: the reference never deletes a GaugeVec child.
+func (c *Ctx) Expire(olderThanUs uint64) (uint64, error) {
+	var n C.uint64_t
+	rc := C.kgx_expire(c.p, C.uint64_t(olderThanUs), &n)
+	return uint64(n), c.err(rc)
+}
+
 // Render returns the text exposition; buf is reused when large enough.
 func (c *Ctx) Render(buf []byte) ([]byte, error) {
 	for {

@@ -224,6 +224,17 @@ int kgx_ingest_nvml_x(kgx_ctx* ctx, const kgx_nvml_process_info* infos, const ui
  * No-op error KGX_E_STATE in R modes, whose series never reset. */
 int kgx_reset_window(kgx_ctx* ctx);
 
+/* X mode: explicit staleness policy.  The reference
+ * keeps a series for ever once it has been Set (main.go has no Delete/Reset,
+ * rule a10) and the R modes stay faithful to that: there this call returns
+ * KGX_E_STATE.  In X mode it drops every series whose newest sample is older
+ * than `older_than_ts_us` (same clock as kgx_cols.ts_us): the series leaves the
+ * exposition, its window state is forgotten, and its place in the series
+ * index, label text and render tiles is reclaimed; a later sample for the same
+ * key starts a new series from zero.  *n_expired (may be NULL) = exported
+ * series dropped.  Nothing happens unless the embedder calls it. */
+int kgx_expire(kgx_ctx* ctx, uint64_t older_than_ts_us, uint64_t* n_expired);
+
 /* Render the Prometheus text exposition (format 0.0.4) of the current state
  * into ctx-owned device memory.  Replaces what promhttp.HandlerFor serves at
  * main.go:69-71 (Registry.Gather + expfmt text encoder).  One body per node,

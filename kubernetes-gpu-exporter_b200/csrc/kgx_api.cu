@@ -897,6 +897,33 @@ int kgx_reset_window(kgx_ctx* c) {
   return KGX_OK;
 }
 
+int kgx_expire(kgx_ctx* c, uint64_t older_than_ts_us, uint64_t* n_expired) {
+  if (!c) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  if (n_expired) *n_expired = 0;
+  if (c->mode != KGX_MODE_X) return fail(c, KGX_E_STATE, "R modes never expire a series: main.go has no Delete/Reset");
+  if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_expire before kgx_set_table");
+  if (c->n_series == 0) return KGX_OK;
+  unsigned long long* ctr = ptr<unsigned long long>(c->d_counters) + C_TICKET + 2;  // two spare counter words
+  KGX_CUDA(c, cudaMemsetAsync(ctr, 0, 16, c->stream));
+  {
+    Timed tm(c, KGX_K_INDEX);
+    const DevAcc a = acc_view(c);
+    k_mark_expired<<<cdiv(c->n_series, 256), 256, 0, c->stream>>>(ptr<uint32_t>(c->d_ser_slot), c->n_series, a.last_ts, a.count,
+                                                                 older_than_ts_us, ptr<uint2>(c->d_bm), ctr);
+    tm.launches(1);
+    KGX_TRY(launch_check(c, "k_mark_expired"));
+  }
+  unsigned long long out[2] = {0, 0};
+  KGX_CUDA(c, cudaMemcpyAsync(out, ctr, 16, cudaMemcpyDeviceToHost, c->stream));
+  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (n_expired) *n_expired = out[0];
+  if (out[1] == 0) return KGX_OK;
+  c->rendered = false;
+  return rebuild_index(c);  // re-rank the survivors, move their state, re-materialise labels and tiles
+}
+
 int kgx_render_device(kgx_ctx* c, size_t* len) {
   if (!c) return KGX_E_INVAL;
   std::lock_guard<std::mutex> g(c->mu);

@@ -279,8 +279,22 @@ __global__ void k_remap(const uint32_t* old_slot, uint32_t n_old, const uint2* b
                         const unsigned long long* const* old_arr, unsigned long long* const* new_arr) {
   const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= n_old) return;
-  const uint32_t nr = rank_of(bm, old_slot[r]);
+  const uint32_t s = old_slot[r];
+  if (!((bm[s >> 5].x >> (s & 31)) & 1u)) return;  // the series was expired (kgx_expire): its state is dropped
+  const uint32_t nr = rank_of(bm, s);
   for (int k = 0; k < n_arrays; ++k) new_arr[k][nr] = old_arr[k][r];
+}
+
+// X mode, explicit expiry: take every series whose newest sample is older than `cutoff` out of the series index.
+// out[0] counts the ones that were exported (had samples in the window), out[1] all of them.
+__global__ void k_mark_expired(const uint32_t* ser_slot, uint32_t n_series, const unsigned long long* last_ts,
+                               const unsigned long long* count, unsigned long long cutoff, uint2* bm, unsigned long long* out) {
+  const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n_series || last_ts[r] >= cutoff) return;
+  const uint32_t s = ser_slot[r];
+  atomicAnd(&bm[s >> 5].x, ~(1u << (s & 31)));
+  if (count[r]) atomicAdd(&out[0], 1ull);
+  atomicAdd(&out[1], 1ull);
 }
 
 __global__ void k_node_ranks(const uint2* bm, const uint32_t* node_slot_base, uint32_t n_nodes, uint32_t n_slots,

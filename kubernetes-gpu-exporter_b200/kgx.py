@@ -15,7 +15,7 @@ _LIB = None
 
 EXPORTS = [
     "kgx_abi_version", "kgx_strerror", "kgx_last_error", "kgx_create", "kgx_destroy", "kgx_set_table", "kgx_ingest",
-    "kgx_ingest_device", "kgx_ingest_nvml", "kgx_ingest_nvml_x", "kgx_reset_window", "kgx_render_device", "kgx_render", "kgx_render_begin", "kgx_render_end", "kgx_body_device", "kgx_body_offsets",
+    "kgx_ingest_device", "kgx_ingest_nvml", "kgx_ingest_nvml_x", "kgx_reset_window", "kgx_expire", "kgx_render_device", "kgx_render", "kgx_render_begin", "kgx_render_end", "kgx_body_device", "kgx_body_offsets",
     "kgx_read_values", "kgx_family_count", "kgx_family_info", "kgx_slot_labels", "kgx_format_values", "kgx_host_alloc",
     "kgx_host_free", "kgx_get_stats", "kgx_get_profile", "kgx_profile_reset", "kgx_set_profile", "kgx_sync",
 ]
@@ -45,6 +45,7 @@ def lib():
         L.kgx_ingest.argtypes = [vp, C.POINTER(abi.kgx_cols)]
         L.kgx_ingest_device.argtypes = [vp, C.POINTER(abi.kgx_cols)]
         L.kgx_reset_window.argtypes = [vp]
+        L.kgx_expire.argtypes = [vp, C.c_uint64, C.POINTER(C.c_uint64)]
         L.kgx_ingest_nvml.argtypes = [vp, vp, abi.u64p, abi.u64p]
         L.kgx_ingest_nvml_x.argtypes = [vp, vp, abi.u64p, vp, abi.u64p, abi.u64p]
         L.kgx_render_device.argtypes = [vp, C.POINTER(C.c_size_t)]
@@ -155,6 +156,12 @@ class Kgx:
 
     def reset_window(self):
         self._chk(lib().kgx_reset_window(self._h))
+
+    def expire(self, older_than_ts_us):
+        """X mode: drop the series whose newest sample is older than the cutoff; returns how many exported series went."""
+        n = C.c_uint64()
+        self._chk(lib().kgx_expire(self._h, int(older_than_ts_us), C.byref(n)))
+        return n.value
 
     def render_device(self):
         n = C.c_size_t()

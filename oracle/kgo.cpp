@@ -329,6 +329,17 @@ int kgo_reset_window(kgo_ctx* c) {
   return KGX_OK;
 }
 
+int kgo_expire(kgo_ctx* c, uint64_t older_than_ts_us, uint64_t* n_expired) {
+  if (!c) return KGX_E_INVAL;
+  if (n_expired) *n_expired = 0;
+  if (c->mode != KGX_MODE_X) return KGX_E_STATE;
+  uint64_t n = 0;
+  for (Acc& a : c->acc)
+    if (a.count && a.last_ts < older_than_ts_us) { a = Acc(); ++n; }
+  if (n_expired) *n_expired = n;
+  return KGX_OK;
+}
+
 int kgo_render(kgo_ctx* c, const uint8_t** out, size_t* len) {
   if (!c || !out || !len) return KGX_E_INVAL;
   if (!c->have_table) return KGX_E_STATE;

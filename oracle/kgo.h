@@ -41,6 +41,9 @@ void kgo_destroy(kgo_ctx*);
 int kgo_set_table(kgo_ctx*, const kgx_table*);
 int kgo_ingest(kgo_ctx*, const kgx_cols*);
 int kgo_reset_window(kgo_ctx*);
+/* X mode, explicit expiry (mirrors kgx_expire): series whose newest sample is older than the
+ * cutoff stop being exported and lose their window state.  R modes: KGX_E_STATE (main.go never deletes). */
+int kgo_expire(kgo_ctx*, uint64_t older_than_ts_us, uint64_t* n_expired);
 /* Render; *out stays valid until the next call on the ctx. */
 int kgo_render(kgo_ctx*, const uint8_t** out, size_t* len);
 int kgo_body_offsets(kgo_ctx*, uint64_t* off, size_t n);

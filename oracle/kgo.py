@@ -37,6 +37,7 @@ def lib():
         L.kgo_set_table.argtypes = [C.c_void_p, C.POINTER(abi.kgx_table)]
         L.kgo_ingest.argtypes = [C.c_void_p, C.POINTER(abi.kgx_cols)]
         L.kgo_reset_window.argtypes = [C.c_void_p]
+        L.kgo_expire.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
         L.kgo_render.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
         L.kgo_body_offsets.argtypes = [C.c_void_p, abi.u64p, C.c_size_t]
         L.kgo_read_values.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.c_size_t, C.POINTER(C.c_size_t)]
@@ -108,6 +109,11 @@ class Oracle:
 
     def reset_window(self):
         self._chk(lib().kgo_reset_window(self._h))
+
+    def expire(self, older_than_ts_us):
+        n = C.c_uint64()
+        self._chk(lib().kgo_expire(self._h, int(older_than_ts_us), C.byref(n)))
+        return n.value
 
     def render(self, copy=True):
         """The body as bytes; with copy=False only its length (bodies beyond 2 GB)."""

@@ -207,6 +207,52 @@ def test_x_window_of_scrapes_and_reset(kgo):
     assert len(_same(g, o)) > 0
 
 
+def test_x_explicit_expiry(kgo):
+    """kgx_expire: X-mode series whose newest sample is older than the cutoff leave the exposition and the index;
+    R modes refuse (the reference never deletes a child)."""
+    f = Fleet(n_nodes=5, pods=48, procs=400, seed=0xB200 + 9, scrapes=4)
+    t = f.table(MODE_X)
+    g, o = _pair(kgo, MODE_X, threads=2)
+    g.set_table(t); o.set_table(t)
+    base = 1_790_000_000_000_000  # fleet.py: scrape k is stamped base + 30 s * k (+ < 1 s of jitter)
+
+    def part(s, keep):
+        return Cols(pid=s.pid[keep], gpu=s.gpu[keep], used=s.used[keep], node=s.node[keep], sm_util=s.sm_util[keep],
+                    mem_util=s.mem_util[keep], ts_us=s.ts_us[keep], gpu_total=s.gpu_total)
+
+    s = f.scrape(0)
+    g.ingest(s); o.ingest(s)
+    s = f.scrape(1)
+    s = part(s, (s.pid % 4) != 0)  # a quarter of the processes is gone by the second scrape
+    g.ingest(s); o.ingest(s)
+    _same(g, o)
+    n0 = g.stats()["n_series"]
+    assert g.expire(0) == o.expire(0) == 0
+    ng, no = g.expire(base + 30_000_000), o.expire(base + 30_000_000)
+    assert ng == no and 0 < ng < n0
+    assert len(_same(g, o)) > 0
+    assert g.stats()["n_series"] == n0 - ng == o.series_count()
+    s = f.scrape(2)  # the expired keys come back: new series, counted from zero
+    g.ingest(s); o.ingest(s)
+    _same(g, o)
+    for fam in range(g.family_count()):
+        assert np.array_equal(g.read_values(fam), o.read_values(fam))
+    total = o.series_count()
+    ng, no = g.expire(2**63), o.expire(2**63)
+    assert ng == no == total
+    assert _same(g, o) == b"" and g.stats()["n_series"] == 0
+    s = f.scrape(3)
+    g.ingest(s); o.ingest(s)
+    assert len(_same(g, o)) > 0
+    g.reset_window(); o.reset_window()
+    assert g.expire(1) == o.expire(1) == 0  # nothing exported goes, but the emptied series leave the index
+    assert g.stats()["n_series"] == 0 and _same(g, o) == b""
+    gr = kgx.Kgx(MODE_R_INTENDED)
+    gr.set_table(f.table(MODE_R_INTENDED))
+    with pytest.raises(kgx.KgxError):
+        gr.expire(1)
+
+
 def test_r_staleness_over_cycles(kgo):
     f = Fleet(n_nodes=3, pods=40, procs=300, seed=0xB200 + 5)
     g, o = _pair(kgo, MODE_R_INTENDED)
