@@ -319,6 +319,10 @@ int rebuild_index(kgx_ctx* c) {
   }
   c->n_tiles = uint32_t(tiles.size());
   KGX_TRY(upload(c, c->d_tiles, tiles.data(), tiles.size()));
+  if (c->n_tiles) {
+    k_tile_labels<<<cdiv(c->n_tiles, 256), 256, 0, c->stream>>>(ptr<Tile>(c->d_tiles), c->n_tiles, ptr<unsigned long long>(c->d_lbl_off));
+    tm.launches(1);
+  }
   KGX_TRY(dev_reserve(c, c->d_tile_state, size_t(c->n_tiles) * 8 + 8));
   // R modes: every series has a value, so a node is live iff it has series
   if (c->mode != KGX_MODE_X) {

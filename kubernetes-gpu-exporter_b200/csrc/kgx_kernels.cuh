@@ -330,14 +330,25 @@ struct FamMeta {
 };
 constexpr int kMaxFamilies = 8;
 
-struct Tile {
+struct __align__(16) Tile {
   uint32_t first;   // rank of the first series
   uint32_t node;
   uint16_t count;   // series in the tile
   uint8_t family;
   uint8_t flags;    // bit0: first tile of (node, family): carries the header
                     // bit1: first tile of the node: records the body offset
+  uint32_t pad_;
+  // byte range of the tile's label text in the series label blob (= lbl_off[first], lbl_off[first + count]): kept in
+  // the descriptor so that the writer's "ticket -> descriptor -> label copy" chain is two memory round trips, not three
+  unsigned long long lbl0, lbl1;
 };
+static_assert(sizeof(Tile) == 32, "Tile is two 16-byte loads");
+__global__ void k_tile_labels(Tile* tiles, uint32_t n_tiles, const unsigned long long* lbl_off) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_tiles) return;
+  tiles[t].lbl0 = lbl_off[tiles[t].first];
+  tiles[t].lbl1 = lbl_off[tiles[t].first + tiles[t].count];
+}
 
 struct DevRender {
   const FamMeta* fam;  // [n_families], device global memory (one schema per ctx)

@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
     nt = __shfl_sync(0xffffffffu, nt, 0);
     if (nt < R.n_tiles && lane == 0) {
       const Tile d = R.tiles[nt];
-      const unsigned long long L0 = R.lbl_off[d.first], L1 = R.lbl_off[d.first + d.count];
+      const unsigned long long L0 = d.lbl0, L1 = d.lbl1;
       const unsigned long long g0 = L0 & ~127ull;  // whole 128-byte lines
       const uint32_t bytes = uint32_t(((L1 + 15ull) & ~15ull) - g0);
       if (bytes) {
