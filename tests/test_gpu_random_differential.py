@@ -74,6 +74,9 @@ def test_random_sequences_match_the_oracle(kgo, mode):
                 g.set_table(t); o.set_table(t)
             elif op == 1 and mode == MODE_X:
                 g.reset_window(); o.reset_window()
+            elif op == 2 and mode == MODE_X:
+                cut = int(rng.integers(0, 1 << 50))   # explicit expiry: series whose newest sample is older go
+                assert g.expire(cut) == o.expire(cut)
             else:
                 c = _cols(rng, n_nodes, G, grouped=bool(rng.integers(0, 2)))
                 g.ingest(c); o.ingest(c)
