@@ -294,14 +294,15 @@ def main():
         state = {"k": 0, "pending": False}
 
         def step_e2e():
-            # the call sequence of a pipelined exporter: while body k-1 is still on its way to the host
-            # (kgx_render_begin), scrape k is already copied in and joined; every body is fully delivered
-            # (kgx_render_end) before the next one is rendered, and the last one inside the timed region
+            # the call sequence of a pipelined exporter: while body k-1 is still on its way to the host, scrape k is
+            # copied in, joined and rendered (kgx_render_begin: into the library's second body buffer, its copy
+            # queued behind the one in flight); then body k-1 is awaited (kgx_render_end).  Every body is fully
+            # delivered, the last one inside the timed region (drain).
             g.reset_window()
             g.ingest(hcols)
+            n = g.render_begin(outs[state["k"] % 2])
             if state["pending"]:
                 g.render_end()
-            n = g.render_begin(outs[state["k"] % 2])
             state["k"] += 1
             state["pending"] = True
             return n

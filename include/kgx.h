@@ -277,7 +277,12 @@ int kgx_render_noalloc(kgx_ctx* ctx, uint8_t* d_out, size_t cap, size_t* len);
  * stream; kgx_render_end waits until the bytes are in `out`.  Between the two
  * the caller may already kgx_reset_window / kgx_ingest the next scrape: its
  * host->device copies and kernels overlap the outgoing body on the full-duplex
- * link.  The next render (or table change) waits for a copy still in flight.
+ * link.  kgx_render_begin may also be called while the previous body is still
+ * in flight: the library then renders into a second device buffer (allocated
+ * on first need, same size as the first) and queues the new copy behind the
+ * old one, so the link never idles; kgx_render_end waits for the OLDEST copy in
+ * flight.  At most two may be outstanding (a third begin waits for the first).
+ * kgx_render, kgx_set_table and an index rebuild wait for every copy in flight.
  * The reference serves a scrape and polls concurrently too (main.go:68-72). */
 int kgx_render_begin(kgx_ctx* ctx, uint8_t* out, size_t cap, size_t* len);
 int kgx_render_end(kgx_ctx* ctx);

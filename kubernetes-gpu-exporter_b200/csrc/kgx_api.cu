@@ -37,7 +37,10 @@ struct kgx_ctx {
   cudaStream_t stream = nullptr;
   cudaStream_t copy_stream = nullptr;  // kgx_render_begin: body D2H overlaps the next ingest
   cudaEvent_t ev_rendered = nullptr;
-  bool copy_pending = false;
+  // Bodies leave through two device buffers in turn: while one is still being copied to the host, the next scrape
+  // is rendered into the other (kgx_render_begin).  *_busy: a copy started by kgx_render_begin still reads that buffer.
+  cudaEvent_t ev_copy_out = nullptr, ev_copy_alt = nullptr;
+  bool out_busy = false, alt_busy = false;
   std::mutex mu;
   std::string err;
   int sm_count = 148;
@@ -72,7 +75,7 @@ struct kgx_ctx {
   DBuf d_node_live, d_gpu_total;
   bool have_total = false;
   // render
-  DBuf d_fam, d_tiles, d_tile_state, d_node_body_off, d_out;
+  DBuf d_fam, d_tiles, d_tile_state, d_node_body_off, d_out, d_out_alt;
   uint32_t n_tiles = 0, tile_lines = 0, render_smem = 0;
   bool render_v2 = false;  // second-generation writer (needs metric names of 15..64 bytes)
   RenderLayout lay{};
@@ -82,7 +85,8 @@ struct kgx_ctx {
   std::vector<FamMeta> fam;
   // misc
   DBuf d_counters;
-  unsigned long long* h_counters = nullptr;  // pinned
+  unsigned long long* h_counters = nullptr;  // pinned and mapped: kernels post results here (k_post_words)
+  unsigned long long* h_counters_dev = nullptr;  // its device alias
   DBuf d_cols[8];
   DBuf d_tmp[6];
   uint32_t seq = 0;
@@ -149,9 +153,9 @@ struct Timed {  // CUDA-event bracket around a launch sequence when profiling
   }
 };
 
-// a body copy started by kgx_render_begin still reads d_out: finish it before d_out is rewritten or freed
+// body copies started by kgx_render_begin still read d_out / d_out_alt: finish them before those are rewritten or freed
 void wait_copy(kgx_ctx* c) {
-  if (c->copy_pending) { cudaStreamSynchronize(c->copy_stream); c->copy_pending = false; }
+  if (c->out_busy || c->alt_busy) { cudaStreamSynchronize(c->copy_stream); c->out_busy = c->alt_busy = false; }
 }
 
 int launch_check(kgx_ctx* c, const char* what) {
@@ -346,7 +350,7 @@ void free_table_state(kgx_ctx* c) {
                  &c->d_A_blob, &c->d_B_blob, &c->d_G_blob, &c->d_A_off, &c->d_B_off, &c->d_G_off, &c->d_runs,
                  &c->d_bm, &c->d_pending, &c->d_popc, &c->d_prefix, &c->d_ser_slot, &c->d_ser_a, &c->d_ser_gidx,
                  &c->d_ser_len, &c->d_lbl_off, &c->d_lbl_blob, &c->d_node_ser_off, &c->d_node_live, &c->d_gpu_total,
-                 &c->d_tiles, &c->d_tile_state, &c->d_node_body_off, &c->d_out};
+                 &c->d_tiles, &c->d_tile_state, &c->d_node_body_off, &c->d_out, &c->d_out_alt};
   for (DBuf* b : all) dev_free(c, *b);
   for (auto& b : c->d_acc) dev_free(c, b);
   for (auto& b : c->d_acc_spare) dev_free(c, b);
@@ -561,7 +565,10 @@ int ingest_device_locked(kgx_ctx* c, const kgx_cols* s) {
     tm.launches(1);
     KGX_TRY(launch_check(c, "k_ingest"));
   }
-  KGX_CUDA(c, cudaMemcpyAsync(c->h_counters, ctr, 3 * 8, cudaMemcpyDeviceToHost, c->stream));
+  // the statistics go to mapped host memory by a store, not by a D2H copy: a copy would queue on the device->host
+  // copy engine behind a body that kgx_render_begin may still be sending (tens of ms)
+  k_post_words<<<1, 32, 0, c->stream>>>(ctr, c->h_counters_dev, 3);
+  c->stats.kernel_launches += 1;
   KGX_CUDA(c, cudaStreamSynchronize(c->stream));
   c->stats.n_matched = c->h_counters[C_MATCHED];
   c->stats.n_dropped = c->h_counters[C_DROPPED];
@@ -585,8 +592,8 @@ int ingest_device_locked(kgx_ctx* c, const kgx_cols* s) {
   return KGX_OK;
 }
 
-int render_device_locked(kgx_ctx* c, size_t* len) {
-  wait_copy(c);
+int render_device_locked(kgx_ctx* c, size_t* len, bool keep_copies = false) {
+  if (!keep_copies) wait_copy(c);
   // a scrape may arrive before the first poll cycle (the reference starts its HTTP server first, main.go:68-74):
   // an empty registry gathers nothing, so the body is empty
   if (!c->have_table) { c->last_len = 0; c->rendered = true; if (len) *len = 0; return KGX_OK; }
@@ -614,7 +621,8 @@ int render_device_locked(kgx_ctx* c, size_t* len) {
     tm.launches(1);
     KGX_TRY(launch_check(c, "k_render"));
   }
-  KGX_CUDA(c, cudaMemcpyAsync(c->h_counters + C_TOTAL_LEN, ctr + C_TOTAL_LEN, 8, cudaMemcpyDeviceToHost, c->stream));
+  k_post_words<<<1, 32, 0, c->stream>>>(ctr + C_TOTAL_LEN, c->h_counters_dev + C_TOTAL_LEN, 1);  // see ingest_device_locked
+  c->stats.kernel_launches += 1;
   KGX_CUDA(c, cudaStreamSynchronize(c->stream));
   c->last_len = size_t(c->h_counters[C_TOTAL_LEN]);
   c->rendered = true;
@@ -652,7 +660,8 @@ int kgx_create(int device, const kgx_opts* opts, kgx_ctx** out) {
   else { if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return KGX_E_CUDA; } c->own_stream = true; }
   cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
   build_family_meta(c);
-  if (cudaMallocHost(reinterpret_cast<void**>(&c->h_counters), C_COUNT * 8) != cudaSuccess ||
+  if (cudaHostAlloc(reinterpret_cast<void**>(&c->h_counters), C_COUNT * 8, cudaHostAllocMapped) != cudaSuccess ||
+      cudaHostGetDevicePointer(reinterpret_cast<void**>(&c->h_counters_dev), c->h_counters, 0) != cudaSuccess ||
       dev_reserve(c, c->d_counters, C_COUNT * 8) != KGX_OK) { kgx_destroy(c); return KGX_E_CUDA; }
   cudaMemsetAsync(c->d_counters.p, 0, C_COUNT * 8, c->stream);
   *out = c;
@@ -672,6 +681,8 @@ void kgx_destroy(kgx_ctx* c) {
   if (c->h_counters) cudaFreeHost(c->h_counters);
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->ev_rendered) cudaEventDestroy(c->ev_rendered);
+  if (c->ev_copy_out) cudaEventDestroy(c->ev_copy_out);
+  if (c->ev_copy_alt) cudaEventDestroy(c->ev_copy_alt);
   if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -953,18 +964,33 @@ int kgx_render_begin(kgx_ctx* c, uint8_t* out, size_t cap, size_t* len) {
   if (!c || !len) return KGX_E_INVAL;
   std::lock_guard<std::mutex> g(c->mu);
   cudaSetDevice(c->device);
-  KGX_TRY(render_device_locked(c, len));
+  if (!c->copy_stream) {
+    KGX_CUDA(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    KGX_CUDA(c, cudaEventCreateWithFlags(&c->ev_rendered, cudaEventDisableTiming));
+    KGX_CUDA(c, cudaEventCreateWithFlags(&c->ev_copy_out, cudaEventDisableTiming));
+    KGX_CUDA(c, cudaEventCreateWithFlags(&c->ev_copy_alt, cudaEventDisableTiming));
+  }
+  if (c->out_busy) {  // the previous body is still leaving from d_out: this one is rendered into the other buffer
+    if (c->alt_busy) { KGX_CUDA(c, cudaEventSynchronize(c->ev_copy_alt)); c->alt_busy = false; }  // the one before that
+    if (c->d_out_alt.cap < c->d_out.cap) {
+      dev_free(c, c->d_out_alt);
+      KGX_CUDA(c, cudaMalloc(&c->d_out_alt.p, c->d_out.cap));
+      c->d_out_alt.cap = c->d_out.cap;
+      c->device_bytes += c->d_out.cap;
+    }
+    std::swap(c->d_out, c->d_out_alt);
+    std::swap(c->out_busy, c->alt_busy);
+    std::swap(c->ev_copy_out, c->ev_copy_alt);
+  }
+  KGX_TRY(render_device_locked(c, len, true));
   if (*len > cap) return fail(c, KGX_E_NOSPACE, "output buffer too small");
   if (*len) {
     if (!out) return fail(c, KGX_E_INVAL, "null output buffer");
-    if (!c->copy_stream) {
-      KGX_CUDA(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
-      KGX_CUDA(c, cudaEventCreateWithFlags(&c->ev_rendered, cudaEventDisableTiming));
-    }
     KGX_CUDA(c, cudaEventRecord(c->ev_rendered, c->stream));
     KGX_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_rendered, 0));
     KGX_CUDA(c, cudaMemcpyAsync(out, c->d_out.p, *len, cudaMemcpyDeviceToHost, c->copy_stream));
-    c->copy_pending = true;
+    KGX_CUDA(c, cudaEventRecord(c->ev_copy_out, c->copy_stream));
+    c->out_busy = true;
   }
   return KGX_OK;
 }
@@ -973,9 +999,12 @@ int kgx_render_end(kgx_ctx* c) {
   if (!c) return KGX_E_INVAL;
   std::lock_guard<std::mutex> g(c->mu);
   cudaSetDevice(c->device);
-  if (c->copy_pending) {
-    KGX_CUDA(c, cudaStreamSynchronize(c->copy_stream));
-    c->copy_pending = false;
+  if (c->alt_busy) {  // the older of two bodies in flight
+    KGX_CUDA(c, cudaEventSynchronize(c->ev_copy_alt));
+    c->alt_busy = false;
+  } else if (c->out_busy) {
+    KGX_CUDA(c, cudaEventSynchronize(c->ev_copy_out));
+    c->out_busy = false;
   }
   return KGX_OK;
 }
@@ -1255,7 +1284,8 @@ extern "C" int kgx_render_noalloc(kgx_ctx* c, uint8_t* d_out, size_t cap, size_t
   else k_render<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, acc_view(c), scratch);
   c->stats.kernel_launches += 1;
   KGX_TRY(launch_check(c, "k_render (noalloc)"));
-  KGX_CUDA(c, cudaMemcpyAsync(c->h_counters + C_TICKET + 1, scratch + C_TOTAL_LEN, 8, cudaMemcpyDeviceToHost, c->stream));
+  k_post_words<<<1, 32, 0, c->stream>>>(scratch + C_TOTAL_LEN, c->h_counters_dev + C_TICKET + 1, 1);
+  c->stats.kernel_launches += 1;
   KGX_CUDA(c, cudaStreamSynchronize(c->stream));
   *len = size_t(c->h_counters[C_TICKET + 1]);
   return KGX_OK;

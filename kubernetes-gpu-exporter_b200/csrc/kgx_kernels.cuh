@@ -557,6 +557,12 @@ __global__ void __launch_bounds__(kUtilThreads) k_join_nvml_util(const unsigned 
   }
 }
 
+// A few result words -> mapped host memory, by plain stores (system scope after the kernel ends): small read-backs
+// must not queue on the device->host copy engine behind a body that is still being sent.
+__global__ void k_post_words(const unsigned long long* src, unsigned long long* mapped_host, int n) {
+  if (int(threadIdx.x) < n) mapped_host[threadIdx.x] = src[threadIdx.x];
+}
+
 // ---- float printer entry (tests) ---------------------------------------------------------
 __global__ void k_format_values(const double* v, uint64_t n, uint8_t* out32) {
   const uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;

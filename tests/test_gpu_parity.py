@@ -397,5 +397,23 @@ def test_pipelined_render_begin_end(kgo):
     g.render_end()
     got.append(bufs[3 % 2][:lens[-1]].tobytes())
     assert got == want
+    # two bodies in flight: scrape k is rendered (into the library's second buffer) while body k-1 is still leaving;
+    # kgx_render_end then delivers the older one.  A table change in between waits for both.
+    want, got, lens = [], [], []
+    for k in range(5):
+        s = f.scrape(k % 4)
+        if k == 3:
+            g.set_table(t); o.set_table(t)
+        g.reset_window(); o.reset_window()
+        g.ingest(s); o.ingest(s)
+        lens.append(g.render_begin(bufs[k % 2]))
+        want.append(o.render())
+        if k:
+            g.render_end()
+            got.append(bufs[(k - 1) % 2][:lens[k - 1]].tobytes())
+    g.render_end()
+    got.append(bufs[4 % 2][:lens[-1]].tobytes())
+    assert got == want
+    assert g.render() == want[-1]  # the synchronous call still works afterwards
     for b in bufs:
         kgx.pinned_free(b)
