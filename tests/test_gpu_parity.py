@@ -253,6 +253,53 @@ def test_x_explicit_expiry(kgo):
         gr.expire(1)
 
 
+def test_concurrent_scrapes_while_polling(kgo):
+    """The reference serves /metrics from HTTP goroutines while its poll loop writes (main.go:68-74).  Here: one
+    writer thread ingesting cycle after cycle, three reader threads rendering all the time.  Every body a reader
+    gets must be exactly the oracle's body after SOME completed cycle (the library serialises calls on a ctx), and
+    the last one must be reachable."""
+    import threading
+    f = Fleet(n_nodes=3, pods=40, procs=300, seed=0xB200 + 11, scrapes=8)
+    t = f.table(MODE_R_INTENDED)
+    g, o = _pair(kgo, MODE_R_INTENDED)
+    g.set_table(t); o.set_table(t)
+    scrapes = [f.scrape(k, x_cols=False) for k in range(8)]
+    want = {o.render()}
+    for rep in range(20):  # the same sequence the writer thread below goes through
+        for s in scrapes:
+            o.ingest(s)
+            want.add(o.render())
+    final = o.render()
+    seen, errors, stop = [set() for _ in range(3)], [], threading.Event()
+
+    def reader(i):
+        try:
+            buf = np.empty(1 << 20, dtype=np.uint8)  # every scraper has its own response buffer (Kgx.render() shares one)
+            while not stop.is_set():
+                n = g.render_into(buf)
+                assert n >= 0
+                b = buf[:n].tobytes()
+                if b not in want:
+                    errors.append("reader %d got a body that matches no completed cycle (%d bytes)" % (i, len(b)))
+                    return
+                seen[i].add(b)
+        except Exception as e:  # noqa: BLE001
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=reader, args=(i,)) for i in range(3)]
+    for th in threads:
+        th.start()
+    for rep in range(20):
+        for s in scrapes:
+            g.ingest(s)
+    stop.set()
+    for th in threads:
+        th.join()
+    assert not errors, errors
+    assert g.render() == final
+    assert sum(len(s) for s in seen) >= 3  # the readers did run
+
+
 def test_r_staleness_over_cycles(kgo):
     f = Fleet(n_nodes=3, pods=40, procs=300, seed=0xB200 + 5)
     g, o = _pair(kgo, MODE_R_INTENDED)
