@@ -187,6 +187,8 @@ class Kgx:
         self._chk(lib().kgx_render_end(self._h))
 
     def render(self):
+        """The body as bytes.  Convenience for single-threaded callers: it reuses one host buffer of this object;
+        concurrent scrapers call render_into() with a buffer each (the C ABI itself is safe to call concurrently)."""
         if self._out is None:
             self._out = np.empty(1 << 16, dtype=np.uint8)
         n = self.render_into(self._out)
