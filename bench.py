@@ -397,9 +397,10 @@ def main():
     # ---- CPU baseline on this box's host cores (rank 0, N=1 only) --------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        n, sec, blen = cpu_leg(args.ref_nodes, 1, 1, 1)
+        cpu_nodes = min(4 * args.ref_nodes, args.nodes)  # ~10 s of single-core work at the default
+        n, sec, blen = cpu_leg(cpu_nodes, 1, 2, 1)
         cpu = {"value": n / sec, "unit": UNIT, "cores": 1, "kind": "port",
-               "sample": "first %d nodes of the fleet (%d samples, %d rendered bytes), 1 warm-up + 1 timed pass" % (args.ref_nodes, n, blen),
+               "sample": "first %d nodes of the fleet (%d samples, %d rendered bytes), 1 warm-up + 2 timed passes" % (cpu_nodes, n, blen),
                "note": "C++ restatement of the Go path (oracle/), not Go: no Go toolchain on the box"}
 
     if rank == 0:
