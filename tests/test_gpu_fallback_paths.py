@@ -38,7 +38,7 @@ print("ok")
 
 
 @pytest.mark.parametrize("env", [{"KGX_RENDER_V1": "1"}, {"KGX_INGEST_V1": "1"}, {"KGX_RENDER_THREADS": "32"},
-                                 {"KGX_RENDER_THREADS": "128"}, {"KGX_RENDER_THREADS": "256"}])
+                                 {"KGX_RENDER_THREADS": "128"}, {"KGX_RENDER_THREADS": "256"}, {"KGX_HOST_TABLE_BUILD": "1"}])
 def test_forced_path_is_byte_exact(env):
     e = dict(os.environ)
     e.update(env)
