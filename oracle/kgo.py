@@ -125,6 +125,14 @@ class Oracle:
             return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(n.value,)).tobytes()
         return C.string_at(p.value, n.value) if n.value else b""
 
+    def render_view(self):
+        """The body as a uint8 array over the oracle's own buffer (no copy; valid until the next render)."""
+        p, n = C.c_void_p(), C.c_size_t()
+        self._chk(lib().kgo_render(self._h, C.byref(p), C.byref(n)))
+        if not n.value:
+            return np.empty(0, dtype=np.uint8)
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(n.value,))
+
     def body_offsets(self):
         off = np.zeros(self.n_nodes + 1, dtype=np.uint64)
         self._chk(lib().kgo_body_offsets(self._h, off.ctypes.data_as(abi.u64p), len(off)))
