@@ -7,8 +7,10 @@ package kgx
 import (
 	"net/http"
 	"strings"
+	"sync"
 
 	"github.com/prometheus/client_golang/prometheus"
+	"github.com/prometheus/common/expfmt"
 )
 
 // Collector satisfies prometheus.Collector with the same fully-qualified
@@ -78,20 +80,33 @@ func labelValues(s string) []string {
 
 // Handler serves the GPU-rendered text exposition; any other negotiated
 // format falls back to the registry path (Collector.Collect).
+//
+// The Content-Type is whatever promhttp itself would send: promhttp.HandlerFor
+// (main.go:69) calls expfmt.Negotiate on the request header and writes the
+// result verbatim, so the same call here gives the same header, including the
+// `escaping=` parameter of common v0.55.0, whatever its default is.
+//
+// net/http serves scrapes concurrently (an HA Prometheus pair, a curl during a
+// scrape), so every request renders into a buffer of its own, taken from a pool
+// and returned only after the body has been written.
 func Handler(ctx *Ctx, fallback http.Handler) http.Handler {
-	var buf []byte
+	pool := sync.Pool{New: func() any { b := make([]byte, 0, 1<<16); return &b }}
 	return http.HandlerFunc(func(w http.ResponseWriter, r *http.Request) {
-		if a := r.Header.Get("Accept"); strings.Contains(a, "protobuf") || strings.Contains(a, "openmetrics") {
+		ct := expfmt.Negotiate(r.Header)
+		if ct.FormatType() != expfmt.TypeTextPlain {
 			fallback.ServeHTTP(w, r)
 			return
 		}
-		body, err := ctx.Render(buf)
+		bp := pool.Get().(*[]byte)
+		body, err := ctx.Render((*bp)[:0])
 		if err != nil { // promhttp.HandlerOpts{} default: HTTP 500
+			pool.Put(bp)
 			http.Error(w, err.Error(), http.StatusInternalServerError)
 			return
 		}
-		buf = body[:0]
-		w.Header().Set("Content-Type", "text/plain; version=0.0.4; charset=utf-8; escaping=values")
+		w.Header().Set("Content-Type", string(ct))
 		w.Write(body)
+		*bp = body[:0] // keep the (possibly grown) backing array for the next scrape
+		pool.Put(bp)
 	})
 }

@@ -164,7 +164,10 @@ void kgx_destroy(kgx_ctx* ctx);
  * KGX_HOST_TABLE_BUILD=1 in the environment at kgx_create the same plan is
  * built by a host routine and uploaded; results are identical.)
  * A table that is rejected (KGX_E_INVAL: ids out of range, label values that
- * are not valid UTF-8, duplicate keys; KGX_E_LIMIT) leaves the ctx as it was.
+ * are not valid UTF-8, duplicate keys; KGX_E_LIMIT on its sizes) leaves the ctx
+ * as it was.  One limit is only known once the old table has been released —
+ * label text of a single series too long for a render tile (about 200 KB):
+ * that KGX_E_LIMIT leaves the ctx without a table (kgx_ingest -> KGX_E_STATE).
  * R modes: series already exported keep their last value across calls, as
  * GaugeVec children do (main.go has no Delete/Reset).  X mode: clears the
  * window. */
@@ -178,7 +181,12 @@ int kgx_set_table(kgx_ctx* ctx, const kgx_table* table);
 int kgx_ingest(kgx_ctx* ctx, const kgx_cols* cols);
 
 /* Same, with every column pointer being DEVICE memory already resident on
- * ctx's GPU (no host<->device copy).  Used to time the device pipeline. */
+ * ctx's GPU (no host<->device copy).  Used to time the device pipeline.
+ * Contract (checked by kgx_ingest on the host, NOT here, where the offsets are
+ * device memory): node_off, when given, has n_nodes+1 entries, starts at 0,
+ * never decreases and ends at n.  Offsets beyond n make the join read past the
+ * columns; rows outside [node_off[0], node_off[n_nodes]) are ignored.  When
+ * both `node` and `node_off` are given, node_off decides the node of a row. */
 int kgx_ingest_device(kgx_ctx* ctx, const kgx_cols* cols);
 
 /* R modes: ingest straight from what NVML hands back, without building columns
@@ -295,6 +303,12 @@ int kgx_body_device(kgx_ctx* ctx, const uint8_t** dptr, size_t* len);
  * off[k]..off[k+1] is node k's /metrics body; off has n_nodes+1 entries. */
 int kgx_body_offsets(kgx_ctx* ctx, uint64_t* off, size_t n);
 
+/* One node's /metrics body out of the last rendered text, copied to host
+ * memory `out`: what the per-node exporter of main.go:69-71 serves for one
+ * scrape.  KGX_E_STATE before any render; KGX_E_NOSPACE with *len = needed if
+ * cap is too small.  The body stays valid until the next render on this ctx. */
+int kgx_body_node(kgx_ctx* ctx, uint32_t node, uint8_t* out, size_t cap, size_t* len);
+
 /* ---- Collector read-back (prometheus.Collector.Collect) ------------------ */
 
 /* Values of family `family` (index in sorted family order) for every series
@@ -308,6 +322,16 @@ int kgx_family_count(kgx_ctx* ctx);
 int kgx_family_info(kgx_ctx* ctx, int family, const char** name,
                     const char** help, const char* const** label_names,
                     int* n_labels);
+/* Label text of EVERY series that has a value, in one call: `blob` receives the
+ * pre-escaped texts `{a="..",b=".."}` back to back in exposition order (the
+ * order of kgx_read_values: entry i belongs to value i of any family), off[i]
+ * .. off[i+1] the bytes of series i (n+1 offsets).  *n and *blob_len receive
+ * the counts; with blob == off == NULL only those are returned, and if a
+ * buffer is too small the call returns KGX_E_NOSPACE with both set.  Two
+ * device->host copies in the common case; replaces one kgx_slot_labels round
+ * trip per series in Collector.Collect (GaugeVec.Collect, main.go:41-42). */
+int kgx_read_labels(kgx_ctx* ctx, char* blob, size_t blob_cap, uint64_t* off,
+                    size_t off_cap, size_t* n, size_t* blob_len);
 /* The pre-escaped label text `{a="..",b=".."}` of a slot; copies at most cap
  * bytes, *len = full length. */
 int kgx_slot_labels(kgx_ctx* ctx, uint32_t slot, char* out, size_t cap,

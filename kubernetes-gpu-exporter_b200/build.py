@@ -18,6 +18,17 @@ def needs_build():
     return any(os.path.getmtime(os.path.join(CSRC, d)) > t for d in DEPS)
 
 
+def build_variant(out_so, extra_flags):
+    """Experiment builds (tools/): the same sources with extra -D flags, into another file."""
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + list(extra_flags) + ["-o", out_so] + [os.path.join(CSRC, s) for s in SOURCES]
+    res = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if res.returncode != 0:
+        print(res.stdout)
+        raise RuntimeError("nvcc failed building " + out_so)
+    return out_so
+
+
 def build(force=False, verbose=False):
     if not force and not needs_build():
         return SO

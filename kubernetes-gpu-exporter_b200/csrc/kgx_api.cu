@@ -82,6 +82,8 @@ struct kgx_ctx {
   int render_grid = 0, render_threads = 64;   // measured best on B200: direct stores, 64-line tiles
   size_t last_len = 0;
   bool rendered = false;
+  std::vector<uint64_t> body_off;  // host copy of the last body's per-node offsets (kgx_body_node), fetched on first use
+  bool body_off_valid = false;
   std::vector<FamMeta> fam;
   // misc
   DBuf d_counters;
@@ -309,6 +311,7 @@ int rebuild_index(kgx_ctx* c) {
   // tiles: (node, family, chunk of series) in output order
   std::vector<Tile> tiles;
   const uint32_t TL = c->tile_lines;
+  if (TL == 0) return fail(c, KGX_E_STATE, "render tile geometry not set");
   const int nf = int(c->fam.size());
   for (uint32_t n = 0; n < NN; ++n) {
     const uint32_t lo = c->node_ser_off[n], hi = c->node_ser_off[n + 1];
@@ -584,7 +587,9 @@ int ingest_device_locked(kgx_ctx* c, const kgx_cols* s) {
   }
   if (!x && c->n_series && s->n) {
     Timed tm(c, KGX_K_FINALIZE);
-    k_finalize_r<<<cdiv(c->n_series, 256), 256, 0, c->stream>>>(acc_view(c), dc, ptr<unsigned long long>(c->d_gpu_total), p.G,
+    DevCols fc = dc;
+    if (grouped) fc.node = nullptr;  // the node of a row is derived the way the join derived it: from node_off
+    k_finalize_r<<<cdiv(c->n_series, 256), 256, 0, c->stream>>>(acc_view(c), fc, ptr<unsigned long long>(c->d_gpu_total), p.G,
                                                                 c->seq, c->n_series, p.n_nodes);
     tm.launches(1);
     KGX_TRY(launch_check(c, "k_finalize_r"));
@@ -596,6 +601,7 @@ int render_device_locked(kgx_ctx* c, size_t* len, bool keep_copies = false) {
   if (!keep_copies) wait_copy(c);
   // a scrape may arrive before the first poll cycle (the reference starts its HTTP server first, main.go:68-74):
   // an empty registry gathers nothing, so the body is empty
+  c->body_off_valid = false;
   if (!c->have_table) { c->last_len = 0; c->rendered = true; if (len) *len = 0; return KGX_OK; }
   if (c->n_tiles == 0) { c->last_len = 0; c->rendered = true; if (len) *len = 0; c->stats.rendered_bytes = 0; return KGX_OK; }
   unsigned long long* ctr = ptr<unsigned long long>(c->d_counters);
@@ -626,8 +632,25 @@ int render_device_locked(kgx_ctx* c, size_t* len, bool keep_copies = false) {
   KGX_CUDA(c, cudaStreamSynchronize(c->stream));
   c->last_len = size_t(c->h_counters[C_TOTAL_LEN]);
   c->rendered = true;
+  c->body_off_valid = false;
   c->stats.rendered_bytes = c->last_len;
   if (len) *len = c->last_len;
+  return KGX_OK;
+}
+
+// per-node offsets of the last rendered body, on the host (cached until the next render)
+int fetch_body_offsets(kgx_ctx* c) {
+  if (c->body_off_valid) return KGX_OK;
+  const size_t NN = c->plan.n_nodes;
+  c->body_off.assign(NN + 1, 0);
+  if (c->have_table && c->n_tiles) {
+    KGX_CUDA(c, cudaMemcpyAsync(c->body_off.data(), c->d_node_body_off.p, (NN + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
+    KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->body_off[NN] = c->last_len;
+    for (size_t k = NN; k-- > 0;)  // nodes without series have an empty body
+      if (c->body_off[k] == ~0ull) c->body_off[k] = c->body_off[k + 1];
+  }
+  c->body_off_valid = true;
   return KGX_OK;
 }
 
@@ -707,8 +730,9 @@ int kgx_set_table(kgx_ctx* c, const kgx_table* table) {
     KGX_TRY(set_table_device(c, table, &cd));
     const auto t1 = now();
     reset_table_state(c);
-    c->have_table = true;
+    c->have_table = false;  // the old table's buffers are gone; the new one counts only once its geometry is set
     KGX_TRY(finish_plan(c));
+    c->have_table = true;
     c->stats.n_slots = c->plan.n_slots;
     if (cd.n) {  // R modes: series that already had a value keep it (main.go never deletes a GaugeVec child)
       k_set_bits<<<cdiv(cd.n, 256), 256, 0, c->stream>>>(cd.slot, cd.n, ptr<uint32_t>(c->d_pending));
@@ -743,9 +767,10 @@ int kgx_set_table(kgx_ctx* c, const kgx_table* table) {
   const auto t2 = now();
   reset_table_state(c);
   c->plan = std::move(np);
-  c->have_table = true;
+  c->have_table = false;  // see the device-build branch
   KGX_TRY(upload_plan(c));
   KGX_TRY(finish_plan(c));
+  c->have_table = true;
   const auto t3 = now();
   c->stats.n_slots = c->plan.n_slots;
   if (!carried.empty()) {
@@ -1022,14 +1047,28 @@ int kgx_body_offsets(kgx_ctx* c, uint64_t* off, size_t n) {
   std::lock_guard<std::mutex> g(c->mu);
   cudaSetDevice(c->device);
   if (!c->rendered) return fail(c, KGX_E_STATE, "no rendered body");
-  const size_t NN = c->plan.n_nodes;
-  if (n != NN + 1) return fail(c, KGX_E_INVAL, "offset array must have n_nodes+1 entries");
-  if (c->n_tiles == 0) { std::fill(off, off + n, 0); return KGX_OK; }
-  KGX_CUDA(c, cudaMemcpyAsync(off, c->d_node_body_off.p, n * 8, cudaMemcpyDeviceToHost, c->stream));
-  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
-  off[NN] = c->last_len;
-  for (size_t k = NN; k-- > 0;)  // nodes without series have an empty body
-    if (off[k] == ~0ull) off[k] = off[k + 1];
+  if (n != size_t(c->plan.n_nodes) + 1) return fail(c, KGX_E_INVAL, "offset array must have n_nodes+1 entries");
+  KGX_TRY(fetch_body_offsets(c));
+  std::copy(c->body_off.begin(), c->body_off.end(), off);
+  return KGX_OK;
+}
+
+int kgx_body_node(kgx_ctx* c, uint32_t node, uint8_t* out, size_t cap, size_t* len) {
+  if (!c || !len) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  if (!c->rendered) return fail(c, KGX_E_STATE, "no rendered body");
+  if (!c->have_table) { *len = 0; return KGX_OK; }  // nothing registered yet: every node's body is empty
+  if (node >= c->plan.n_nodes) return fail(c, KGX_E_INVAL, "node out of range");
+  KGX_TRY(fetch_body_offsets(c));
+  const uint64_t lo = c->body_off[node], hi = c->body_off[size_t(node) + 1];
+  *len = size_t(hi - lo);
+  if (*len > cap) return fail(c, KGX_E_NOSPACE, "output buffer too small");
+  if (*len) {
+    if (!out) return fail(c, KGX_E_INVAL, "null output buffer");
+    KGX_CUDA(c, cudaMemcpyAsync(out, ptr<uint8_t>(c->d_out) + lo, *len, cudaMemcpyDeviceToHost, c->stream));
+    KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
   return KGX_OK;
 }
 
@@ -1079,6 +1118,55 @@ int kgx_read_values(kgx_ctx* c, int family, double* values, uint32_t* slots, siz
   }
   *n_out = n;
   return n <= cap ? KGX_OK : fail(c, KGX_E_NOSPACE, "value buffer too small");
+}
+
+int kgx_read_labels(kgx_ctx* c, char* blob, size_t blob_cap, uint64_t* off, size_t off_cap, size_t* n_out, size_t* blob_len) {
+  if (!c || !n_out || !blob_len) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  *n_out = 0; *blob_len = 0;
+  if (!c->have_table || !c->n_series) { if (off && off_cap) off[0] = 0; return KGX_OK; }
+  const uint32_t S = c->n_series;
+  // which series carry a value (the same rule as kgx_read_values; it does not depend on the family)
+  KGX_TRY(dev_reserve(c, c->d_tmp[1], size_t(S) * 8));
+  KGX_TRY(dev_reserve(c, c->d_tmp[2], size_t(S)));
+  DevRender R{};
+  R.ser_gidx = ptr<uint32_t>(c->d_ser_gidx); R.gpu_total = ptr<unsigned long long>(c->d_gpu_total);
+  k_values<<<cdiv(S, 256), 256, 0, c->stream>>>(R, acc_view(c), c->fam[0].kind, S, ptr<double>(c->d_tmp[1]), ptr<uint8_t>(c->d_tmp[2]));
+  c->stats.kernel_launches += 1;
+  KGX_TRY(launch_check(c, "k_values"));
+  std::vector<uint8_t> live(S);
+  std::vector<uint64_t> all_off(size_t(S) + 1);
+  KGX_CUDA(c, cudaMemcpyAsync(live.data(), c->d_tmp[2].p, S, cudaMemcpyDeviceToHost, c->stream));
+  KGX_CUDA(c, cudaMemcpyAsync(all_off.data(), c->d_lbl_off.p, (size_t(S) + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
+  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  size_t n = 0, bytes = 0;
+  for (uint32_t r = 0; r < S; ++r)
+    if (live[r]) { ++n; bytes += size_t(all_off[r + 1] - all_off[r]); }
+  *n_out = n; *blob_len = bytes;
+  if (!blob && !off) return KGX_OK;  // size query
+  if (!blob || !off || blob_cap < bytes || off_cap < n + 1) return fail(c, KGX_E_NOSPACE, "label buffers too small (sizes returned)");
+  if (n == S) {  // every series has a value: the device blob is already the answer, in exposition order
+    std::copy(all_off.begin(), all_off.end(), off);
+    if (bytes) KGX_CUDA(c, cudaMemcpyAsync(blob, c->d_lbl_blob.p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+    return KGX_OK;
+  }
+  // some series of the index carry no value in this window: copy maximal runs of live series
+  size_t k = 0, at = 0;
+  for (uint32_t r = 0; r < S;) {
+    if (!live[r]) { ++r; continue; }
+    uint32_t e = r;
+    while (e < S && live[e]) ++e;
+    const size_t run = size_t(all_off[e] - all_off[r]);
+    if (run) KGX_CUDA(c, cudaMemcpyAsync(blob + at, ptr<uint8_t>(c->d_lbl_blob) + all_off[r], run, cudaMemcpyDeviceToHost, c->stream));
+    for (uint32_t q = r; q < e; ++q) off[k++] = at + (all_off[q] - all_off[r]);
+    at += run;
+    r = e;
+  }
+  off[k] = at;
+  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  return KGX_OK;
 }
 
 int kgx_slot_labels(kgx_ctx* c, uint32_t slot, char* out, size_t cap, size_t* len) {
@@ -1200,6 +1288,15 @@ int kgx_profile_reset(kgx_ctx* c) {
   c->prof = kgx_profile{};
   return KGX_OK;
 }
+
+#ifdef KGX_PHASE_CLOCKS
+// experiment builds only (tools/phase_clocks.py): cycles thread 0 of every writer CTA spent in each phase of a tile
+int kgx_debug_phase_clocks(unsigned long long* out16, int reset) {
+  if (out16 && cudaMemcpyFromSymbol(out16, kgx::g_phase_clk, 16 * 8) != cudaSuccess) return KGX_E_CUDA;
+  if (reset) { unsigned long long z[16] = {}; if (cudaMemcpyToSymbol(kgx::g_phase_clk, z, sizeof z) != cudaSuccess) return KGX_E_CUDA; }
+  return KGX_OK;
+}
+#endif
 
 }  // extern "C"
 

@@ -42,6 +42,10 @@ struct RenderLayout {  // byte offsets inside dynamic shared memory (all 16-alig
 };
 constexpr uint32_t kSlotBytes = 28;  // 7 words: odd word stride -> conflict-free byte stores
 constexpr uint32_t kNameStride = 96;
+#ifndef KGX_LOOKBACK
+#define KGX_LOOKBACK 1
+#endif
+constexpr int kLookBack = KGX_LOOKBACK;  // predecessors per lane and look-back step
 
 __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
   uint32_t v;
@@ -62,6 +66,17 @@ __device__ __forceinline__ uint4 merge16(uint4 lo, uint4 hi, uint32_t e) {
   return make_uint4((lo.x & m.x) | (hi.x & ~m.x), (lo.y & m.y) | (hi.y & ~m.y), (lo.z & m.z) | (hi.z & ~m.z),
                     (lo.w & m.w) | (hi.w & ~m.w));
 }
+
+#ifdef KGX_PHASE_CLOCKS  // experiment build only (tools/phase_clocks.py): where a tile's time goes, thread 0's view
+__device__ unsigned long long g_phase_clk[16];
+#define KGX_PC_DECL unsigned long long pc_acc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; long long pc_t = clock64(); unsigned long long pc_tiles = 0
+#define KGX_PC(i) do { if (tid == 0) { const long long n_ = clock64(); pc_acc[i] += (unsigned long long)(n_ - pc_t); pc_t = n_; } } while (0)
+#define KGX_PC_FLUSH do { if (tid == 0) { for (int i_ = 0; i_ < 10; ++i_) atomicAdd(&g_phase_clk[i_], pc_acc[i_]); atomicAdd(&g_phase_clk[10], pc_tiles); } } while (0)
+#else
+#define KGX_PC_DECL
+#define KGX_PC(i)
+#define KGX_PC_FLUSH
+#endif
 
 template <int THREADS>
 __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout lay, DevAcc acc, unsigned long long* counters) {
@@ -115,9 +130,10 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
   __syncthreads();
 
   uint32_t parity = 0;
+  KGX_PC_DECL;
   for (;;) {
     const uint32_t t = s_next;
-    if (t >= R.n_tiles) return;
+    if (t >= R.n_tiles) { KGX_PC_FLUSH; return; }
     const Tile tile = s_desc;
     const uint32_t l0 = s_l0;
     const FamMeta& fm = R.fam[tile.family];
@@ -129,7 +145,11 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
     if (tid < tile.count) {
       const uint32_t r = tile.first + tid;
       lbl_len = R.ser_len[r];  // 4 bytes per series; offsets inside the tile come from the CTA scan below
-      const double v = series_value(fm.kind, acc, R, r, live);
+      double v = series_value(fm.kind, acc, R, r, live);
+#ifdef KGX_PHASE_CLOCKS
+      asm volatile("mov.b64 %0, %0;" : "+d"(v));
+      KGX_PC(0);  // state loads
+#endif
       if (live) {
         uint8_t* sp = smem + lay.slots + tid * kSlotBytes;
         sp[0] = ' ';
@@ -138,6 +158,7 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
         len = name_len + lbl_len + vlen + 2;
       }
     }
+    KGX_PC(1);  // format
     const uint32_t hdr = ((tile.flags & 1) && acc.node_live[tile.node] != 0) ? fm.header_len : 0;
     // ---- exclusive scan over the CTA, three fields at once: output bytes (24 bits), label bytes of
     // every series, printed or not (24 bits), lines printed (16 bits)
@@ -146,6 +167,7 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
     for (int o = 1; o < 32; o <<= 1) { unsigned long long u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
     if (lane == 31) s_scan[wid] = inc;
     __syncthreads();  // (1) also: everyone has read s_next / s_desc / s_l0
+    KGX_PC(2);  // scan barrier
     unsigned long long woff = 0, all = 0;
     for (int k = 0; k < THREADS / 32; ++k) { if (k < int(wid)) woff += s_scan[k]; all += s_scan[k]; }
     const unsigned long long exc = woff + inc - mine;
@@ -159,21 +181,38 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
     if (tid == 0 && t > 0) atomicExch(&R.tile_state[t], kStAgg | total);
     unsigned long long base = 0;
     if (t > 0) {
-      long long p = (long long)t - 1 - lane;  // lane 0 looks at the direct predecessor
+      // One step of the walk covers 32 * kLookBack predecessors: kLookBack coalesced loads of 32 consecutive look-back
+      // words each (lane 0 of load 0 is the direct predecessor), all in flight together.  With thousands of tiles in
+      // flight the nearest tile that already knows its prefix is hundreds of tickets back, so a 32-tile step meant
+      // ~20 dependent L2 round trips per tile (profiles/README.md, round 2).
+      long long p = (long long)t - 1 - lane;
       for (;;) {
-        unsigned long long s = kStPrefix;     // before tile 0: an inclusive prefix of zero
-        if (p >= 0) {
-          do { s = *(volatile unsigned long long*)&R.tile_state[p]; } while ((s & kStMask) == 0);
+        unsigned long long st[kLookBack];
+#pragma unroll
+        for (int k = 0; k < kLookBack; ++k) {
+          const long long q = p - 32 * k;
+          st[k] = q >= 0 ? (unsigned long long)*(volatile unsigned long long*)&R.tile_state[q] : (unsigned long long)kStPrefix;  // before tile 0: prefix 0
         }
-        const uint32_t pfx = __ballot_sync(0xffffffffu, (s & kStMask) == kStPrefix);
-        const uint32_t first = pfx ? uint32_t(__ffs(pfx) - 1) : 32u;
-        unsigned long long v = lane <= first ? (s & ~kStMask) : 0ull;
+        unsigned long long v = 0;
+        bool found = false;
+#pragma unroll
+        for (int k = 0; k < kLookBack; ++k) {
+          const long long q = p - 32 * k;
+          while ((st[k] & kStMask) == 0) st[k] = *(volatile unsigned long long*)&R.tile_state[q];  // not published yet
+          const uint32_t pfx = __ballot_sync(0xffffffffu, (st[k] & kStMask) == kStPrefix);
+          if (!found) {  // warp-uniform
+            const uint32_t first = pfx ? uint32_t(__ffs(pfx) - 1) : 32u;
+            if (lane <= first) v += st[k] & ~kStMask;
+            found = pfx != 0;
+          }
+        }
         for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
         base += v;
-        if (pfx) break;
-        p -= 32;
+        if (found) break;
+        p -= 32 * kLookBack;
       }
     }
+    KGX_PC(3);  // look-back
     if (tid == 0) {
       atomicExch(&R.tile_state[t], kStPrefix | (base + total));
       if (tile.flags & 2) R.node_body_off[tile.node] = base;
@@ -185,6 +224,7 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
     if (hdr) for (uint32_t i = tid; i < hdr; i += THREADS) gtile[i] = fm.header[i];
     mbar_wait(bar, parity);  // staged labels have landed (issued a whole tile ago)
     parity ^= 1;
+    KGX_PC(4);  // header + label wait
     // ---- pass 2: stream my line to the output as 16-byte chunks aligned to the global address
     if (live) {
       const uint32_t g = sh + off;                                              // first byte of my line (position)
@@ -235,10 +275,17 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
         for (uint32_t q = 0; q < e; ++q) galn[p + q] = sp[q];
       }
     }
+    KGX_PC(5);  // stream my line
     if (tid == 0) tk_next = atomicAdd(&counters[C_TICKET], 1ull);  // in flight while the rest of the CTA finishes its lines
     __syncthreads();             // (2) label stage and value slots are free
+    KGX_PC(6);  // end-of-tile barrier
     if (wid == 0) fetch_next();  // next ticket, descriptor, label copy
+    KGX_PC(7);  // ticket + descriptor
     __syncthreads();             // (3) s_next / s_desc / s_l0 visible
+    KGX_PC(8);
+#ifdef KGX_PHASE_CLOCKS
+    ++pc_tiles;
+#endif
   }
 }
 

@@ -10,13 +10,13 @@ import numpy as np
 from . import abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "csrc", "libkgx.so")
+SO_PATH = os.environ.get("KGX_LIB") or os.path.join(_HERE, "csrc", "libkgx.so")  # KGX_LIB: an experiment build (tools/)
 _LIB = None
 
 EXPORTS = [
     "kgx_abi_version", "kgx_strerror", "kgx_last_error", "kgx_create", "kgx_destroy", "kgx_set_table", "kgx_ingest",
-    "kgx_ingest_device", "kgx_ingest_nvml", "kgx_ingest_nvml_x", "kgx_reset_window", "kgx_expire", "kgx_render_device", "kgx_render", "kgx_render_begin", "kgx_render_end", "kgx_body_device", "kgx_body_offsets",
-    "kgx_read_values", "kgx_family_count", "kgx_family_info", "kgx_slot_labels", "kgx_format_values", "kgx_host_alloc",
+    "kgx_ingest_device", "kgx_ingest_nvml", "kgx_ingest_nvml_x", "kgx_reset_window", "kgx_expire", "kgx_render_device", "kgx_render", "kgx_render_begin", "kgx_render_end", "kgx_body_device", "kgx_body_offsets", "kgx_body_node",
+    "kgx_read_values", "kgx_read_labels", "kgx_render_noalloc", "kgx_family_count", "kgx_family_info", "kgx_slot_labels", "kgx_format_values", "kgx_host_alloc",
     "kgx_host_free", "kgx_get_stats", "kgx_get_profile", "kgx_profile_reset", "kgx_set_profile", "kgx_sync",
 ]
 
@@ -54,6 +54,9 @@ def lib():
         L.kgx_render_end.argtypes = [vp]
         L.kgx_body_device.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]
         L.kgx_body_offsets.argtypes = [vp, abi.u64p, C.c_size_t]
+        L.kgx_body_node.argtypes = [vp, C.c_uint32, vp, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.kgx_read_labels.argtypes = [vp, vp, C.c_size_t, abi.u64p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]
+        L.kgx_render_noalloc.argtypes = [vp, vp, C.c_size_t, C.POINTER(C.c_size_t)]
         L.kgx_read_values.argtypes = [vp, C.c_int, C.POINTER(C.c_double), abi.u32p, C.c_size_t, C.POINTER(C.c_size_t)]
         L.kgx_family_count.argtypes = [vp]
         L.kgx_family_info.argtypes = [vp, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_char_p),
@@ -207,6 +210,16 @@ class Kgx:
         self._chk(lib().kgx_body_offsets(self._h, off.ctypes.data_as(abi.u64p), len(off)))
         return off
 
+    def body_node(self, node):
+        """One node's /metrics body out of the last rendered text (kgx_body_node)."""
+        n = C.c_size_t()
+        rc = lib().kgx_body_node(self._h, int(node), None, 0, C.byref(n))
+        if rc not in (0, abi.KGX_E_NOSPACE):
+            self._chk(rc)
+        out = np.empty(max(1, n.value), dtype=np.uint8)
+        self._chk(lib().kgx_body_node(self._h, int(node), out.ctypes.data, out.nbytes, C.byref(n)))
+        return out[:n.value].tobytes()
+
     def family_count(self):
         return lib().kgx_family_count(self._h)
 
@@ -225,6 +238,16 @@ class Kgx:
         self._chk(lib().kgx_read_values(self._h, family, vals.ctypes.data_as(C.POINTER(C.c_double)),
                                         slots.ctypes.data_as(abi.u32p), len(vals), C.byref(n)))
         return (vals, slots) if with_slots else vals
+
+    def read_labels(self):
+        """(blob, offsets): label text of every series with a value, exposition order (kgx_read_labels)."""
+        n, nb = C.c_size_t(), C.c_size_t()
+        self._chk(lib().kgx_read_labels(self._h, None, 0, None, 0, C.byref(n), C.byref(nb)))
+        blob = np.empty(max(1, nb.value), dtype=np.uint8)
+        off = np.zeros(n.value + 1, dtype=np.uint64)
+        self._chk(lib().kgx_read_labels(self._h, blob.ctypes.data, nb.value, off.ctypes.data_as(abi.u64p), len(off),
+                                        C.byref(n), C.byref(nb)))
+        return blob[:nb.value], off
 
     def slot_labels(self, slot):
         n = C.c_size_t()

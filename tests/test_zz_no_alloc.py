@@ -8,8 +8,12 @@ brings along.
 Checked here, through the C ABI, against the ordinary kgx_render on the same
 context: byte-identical bodies on two calls in a row (the second after the
 state changed, so leftovers of the first call in the shared scratch array
-would show), plus the documented size limits.  Collected last on purpose."""
+would show); that the second call really allocates nothing (the library's own
+accounting and the driver's free-memory figure both stay put); two contexts
+taking turns on the one shared array; the generic writer; and the documented
+size limits.  Collected last on purpose."""
 import ctypes as C
+import os
 
 import numpy as np
 import pytest
@@ -25,7 +29,6 @@ pytestmark = pytest.mark.gpu
 
 def _noalloc(g, buf):
     fn = kgx.lib().kgx_render_noalloc
-    fn.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
     n = C.c_size_t()
     rc = fn(g._h, buf.data_ptr() if buf is not None else None, buf.numel() if buf is not None else 0, C.byref(n))
     return rc, n.value
@@ -52,11 +55,57 @@ def test_noalloc_matches_render_twice_in_a_row(mode):
             g.ingest(s)
         want = g.render()                             # existing entry point
         buf.fill_(0x5a)
+        torch.cuda.synchronize()
+        held, free = g.stats()["device_bytes"], torch.cuda.mem_get_info()[0]
         rc, n = _noalloc(g, buf)
         assert rc == 0, kgx.lib().kgx_last_error(g._h)
+        if k == 1:                                    # the promise itself: nothing was allocated (the first call on a
+            assert g.stats()["device_bytes"] == held  # GPU may still make the driver load the module's data)
+            assert torch.cuda.mem_get_info()[0] == free
         got = buf[:n].cpu().numpy().tobytes()
         assert n == len(want) and got == want         # bytes: exact
         assert g.render() == want                     # and the ordinary path is undisturbed
+
+
+def test_noalloc_two_contexts_take_turns_on_the_shared_array():
+    """Every ctx on a GPU uses the same scratch array.  Two of them, of different shapes, called one after the other
+    (serialised, as the header asks): each call must clear what the other left behind."""
+    build.build()
+    fa = Fleet(n_nodes=7, pods=90, procs=900, seed=0xB200 + 31)
+    fb = Fleet(n_nodes=3, pods=20, procs=150, seed=0xB200 + 32)
+    ga, gb = kgx.Kgx(MODE_X), kgx.Kgx(MODE_R_INTENDED)
+    ga.set_table(fa.table(MODE_X)); gb.set_table(fb.table(MODE_R_INTENDED))
+    ga.ingest(fa.scrape(0)); gb.ingest(fb.scrape(0))
+    wa, wb = ga.render(), gb.render()
+    _, need_a = _noalloc(ga, None)
+    _, need_b = _noalloc(gb, None)
+    buf = torch.empty(max(need_a, need_b), dtype=torch.uint8, device="cuda")
+    for g, want in ((ga, wa), (gb, wb), (gb, wb), (ga, wa), (gb, wb)):
+        buf.fill_(0xa5)
+        rc, n = _noalloc(g, buf)
+        torch.cuda.synchronize()
+        assert rc == 0 and buf[:n].cpu().numpy().tobytes() == want
+
+
+def test_noalloc_generic_writer_path():
+    """KGX_RENDER_V1 (read when the table is installed) selects the generic writer, which schemas with unusual metric
+    names take; the allocation-free entry point must serve that path too."""
+    build.build()
+    f = Fleet(n_nodes=4, pods=30, procs=260, seed=0xB200 + 33)
+    os.environ["KGX_RENDER_V1"] = "1"
+    try:
+        g = kgx.Kgx(MODE_X)
+        g.set_table(f.table(MODE_X))
+    finally:
+        del os.environ["KGX_RENDER_V1"]
+    g.ingest(f.scrape(0))
+    want = g.render()
+    _, need = _noalloc(g, None)
+    buf = torch.empty(need, dtype=torch.uint8, device="cuda")
+    for _ in range(2):
+        buf.fill_(0)
+        rc, n = _noalloc(g, buf)
+        assert rc == 0 and buf[:n].cpu().numpy().tobytes() == want
 
 
 def test_noalloc_rejects_sizes_beyond_its_scratch():
@@ -70,3 +119,12 @@ def test_noalloc_rejects_sizes_beyond_its_scratch():
     assert rc == abi.KGX_E_LIMIT
     assert b"KGX_NOALLOC_MAX_NODES" in kgx.lib().kgx_last_error(g._h)
     assert g.render().startswith(b"# HELP")           # the allocating entry point still serves it
+    # within the node limit but more render tiles than KGX_NOALLOC_MAX_TILES (65 536): 4 000 nodes x 2 families x 10
+    f = Fleet(n_nodes=4000, pods=100, procs=600, seed=0xB200 + 34)
+    g = kgx.Kgx(MODE_R_INTENDED)
+    g.set_table(f.table(MODE_R_INTENDED))
+    g.ingest(f.scrape(0))
+    rc, _ = _noalloc(g, buf)
+    assert rc == abi.KGX_E_LIMIT
+    assert b"KGX_NOALLOC_MAX_TILES" in kgx.lib().kgx_last_error(g._h)
+    assert len(g.render()) > (1 << 20)

@@ -28,10 +28,15 @@ for l in sass:
         lines.append((cur, l.strip()))
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
-h = next(i for i, r in enumerate(rows) if "Source" in r and "Address" in r)
+# the page holds one block per captured launch ("Kernel Name" row, header row, one row per instruction): take the
+# first block of the wanted kernel
+want = re.sub(r"I[A-Z].*$", "", kern)  # "k_render3ILi64" (mangled) -> "k_render3"
+k0 = next(i for i, r in enumerate(rows) if r and r[0] == "Kernel Name" and want in r[1])
+h = next(i for i in range(k0, len(rows)) if "Source" in rows[i] and "Address" in rows[i])
 H = rows[h]
 ii, si, sm = H.index("Instructions Executed"), H.index("Source"), H.index("# Samples")
-body = rows[h + 1:]
+end = next((i for i in range(h + 1, len(rows)) if rows[i] and rows[i][0] in ("Kernel Name", "Address")), len(rows))
+body = rows[h + 1:end]
 if len(body) != len(lines):
     print("warning: %d profiled instructions vs %d disassembled" % (len(body), len(lines)))
 agg = defaultdict(lambda: [0, 0])
