@@ -41,25 +41,33 @@ from kgx_b200.fleet import CONFIGS, Fleet  # noqa: E402
 METRIC = "per-pod samples aggregated+rendered/sec"
 UNIT = "samples/s"
 CFG = 4
+TRAFFIC_CSV = "r02_k_render_raw.csv"  # the `ncu --set full` raw page of the shipped writer (profiles/README.md)
 
 
-def ncu_traffic(kernel_csv):
-    """dram read+write bytes per launch of the dominant kernel, from the committed
-    `ncu --set full` raw page (profiles/); None if the capture is not there."""
+def ncu_traffic(kernel_csv, measured_ms):
+    """(dram read+write bytes per launch of the dominant kernel, note) from the committed `ncu --set full` raw page
+    under profiles/.  A capture of a different kernel version would go stale silently, so the capture's own duration
+    must agree with the duration measured in THIS run within 10 %, or the traffic is withheld (None)."""
     import csv
     path = os.path.join(ROOT, "profiles", kernel_csv)
     if not os.path.exists(path):
-        return None
+        return None, "no capture at profiles/%s" % kernel_csv
     rows = list(csv.reader(open(path)))
     hdr, units, vals = rows[0], rows[1], rows[-1]
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    tscale = {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}
     total = 0.0
     for key in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
         if key not in hdr:
-            return None
+            return None, "capture lacks %s" % key
         i = hdr.index(key)
         total += float(vals[i].replace(",", "")) * scale.get(units[i], 1.0)
-    return total
+    if "gpu__time_duration.sum" in hdr and measured_ms > 0:
+        i = hdr.index("gpu__time_duration.sum")
+        cap_ms = float(vals[i].replace(",", "")) * tscale.get(units[i], 1.0)
+        if abs(cap_ms - measured_ms) / measured_ms > 0.10:
+            return None, "stale capture withheld: profiles/%s ran %.3f ms, this run's kernel %.3f ms" % (kernel_csv, cap_ms, measured_ms)
+    return total, "profiles/%s (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, one launch)" % kernel_csv
 
 
 def peaks():
@@ -157,7 +165,9 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u64/f64", "data": "synthetic",
-        "config": workload_config(CONFIGS[CFG]["n_nodes"]),
+        "config": dict(workload_config(CONFIGS[CFG]["n_nodes"]),
+                       ran="a bounded sample of that workload per step: the first %d of its %d nodes, %d samples (rates compare; "
+                           "the whole fleet would take ~20x longer per step)" % (nodes, CONFIGS[CFG]["n_nodes"], n)),
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample,
                          "note": "C++ restatement of the Go path, not Go: " +
                                  ("go toolchain present but reference deps are not vendored" if go.returncode == 0
@@ -210,6 +220,178 @@ class near_gpu:
         return False
 
 
+def copy_floor(dev, h2d_bytes, d2h_bytes, steps, barrier, world):
+    """What the link alone allows: per step one pinned D2H copy of a body and, the other way at the same time, one
+    pinned H2D copy of a scrape — no kernels, nothing else.  CUDA events on both streams, slower stream counts, max
+    over ranks (all ranks copy concurrently, as they do in the e2e leg)."""
+    import torch
+    import torch.distributed as dist
+    if d2h_bytes <= 0:
+        return None
+    with near_gpu(dev.index):
+        h_out = torch.empty(d2h_bytes, dtype=torch.uint8, pin_memory=True)
+        h_in = torch.empty(max(1, h2d_bytes), dtype=torch.uint8, pin_memory=True)
+        h_out[::4096] = 0
+        h_in[::4096] = 0
+    d_out = torch.empty(d2h_bytes, dtype=torch.uint8, device=dev)
+    d_in = torch.empty(max(1, h2d_bytes), dtype=torch.uint8, device=dev)
+    s_out, s_in = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+
+    def run(k):
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        ev[0].record(s_out); ev[2].record(s_in)
+        for _ in range(k):
+            with torch.cuda.stream(s_out):
+                h_out.copy_(d_out, non_blocking=True)
+            with torch.cuda.stream(s_in):
+                d_in.copy_(h_in, non_blocking=True)
+        ev[1].record(s_out); ev[3].record(s_in)
+        torch.cuda.synchronize()
+        return max(ev[0].elapsed_time(ev[1]), ev[2].elapsed_time(ev[3])) / k
+
+    run(1)
+    barrier()
+    ms = run(steps)
+    barrier()
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    del h_out, h_in, d_out, d_in
+    return float(t.item())
+
+
+def device_cols(cols, dev):
+    """The sample columns resident in HBM (torch owns the buffers): (kgx_cols struct of device pointers, keep-alive)."""
+    import torch
+
+    def dev_t(a):
+        return None if a is None else torch.from_numpy(a.view(np.int64) if a.dtype == np.uint64 else a.view(np.int32)).to(dev)
+
+    keep = {k: dev_t(getattr(cols, k)) for k in ("pid", "gpu", "used", "node", "sm_util", "mem_util", "ts_us", "node_off", "gpu_total")}
+    ds = abi.kgx_cols()
+    ds.n = cols.n
+    for k, t in keep.items():
+        if t is not None:
+            setattr(ds, k, C.cast(t.data_ptr(), abi.u64p if t.dtype == torch.int64 else abi.u32p))
+    return ds, keep
+
+
+def timed_steps(g, ds, stream, steps, warmup, barrier, x_mode=True, clocks=None):
+    """W untimed + K timed passes of the hot path over one resident scrape; CUDA events on the ctx's stream."""
+    import torch
+
+    def step():
+        if x_mode:
+            g.reset_window()
+        g.ingest_device(ds)
+        return g.render_device()
+
+    with torch.cuda.stream(stream):
+        for _ in range(warmup):
+            body_len = step()
+        g.sync()
+        g.profile_reset()
+        launches0 = g.stats()["kernel_launches"]
+        if clocks:
+            clocks.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record(stream)
+        for _ in range(steps):
+            body_len = step()
+        e1.record(stream)
+        barrier()
+    return e0.elapsed_time(e1) / steps, body_len, g.stats()["kernel_launches"] - launches0
+
+
+def sharded_leg(cfg, mode, rank, world, dev, local, steps, warmup, barrier, oracle_nodes=3, whole_body_oracle=False):
+    """Strong scaling: ONE fleet of BASELINE config `cfg` split by node over the ranks (fleetshard.node_range), each
+    rank joins/reduces/renders its own nodes, then the bodies are concatenated in node order on rank 0 (the path's
+    only cross-rank step).  Outside the timed regions the concatenation is checked: every rank's slice
+    against that rank's own checksum, and sampled nodes (or the whole body) byte for byte against the CPU oracle."""
+    import torch
+    import torch.distributed as dist
+    from kgx_b200 import fleetshard, kgx
+    n_total = CONFIGS[cfg]["n_nodes"]
+    lo, hi = fleetshard.node_range(rank, world, n_total)
+    f = Fleet.config(cfg, n_nodes=hi - lo, node_base=lo)
+    table, cols = f.table(mode), f.scrape(0)
+    stream = torch.cuda.Stream(device=dev)
+    g = kgx.Kgx(mode, device=local, stream=stream.cuda_stream, profile=True)
+    g.set_table(table)
+    ds, keep = device_cols(cols, dev)
+    ms, body_len, launches = timed_steps(g, ds, stream, steps, warmup, barrier, x_mode=(mode == MODE_X))
+    ms_max = fleetshard.max_over_ranks(ms, device=dev)
+    prof = g.profile()
+    total_samples = CONFIGS[cfg]["n_nodes"] * CONFIGS[cfg]["procs"]
+    # ---- ordered concatenation on rank 0, timed on the device, max over ranks
+    g.render_device()
+    ptr_, n_ = g.body_device()
+    body = torch.as_tensor(fleetshard.DeviceBytes(ptr_, n_), device=dev) if n_ else torch.empty(0, dtype=torch.uint8, device=dev)
+    lengths, offs = fleetshard.gather_layout(n_, device=dev)
+    root_out = torch.empty(int(offs[-1]), dtype=torch.uint8, device=dev) if rank == 0 else None
+    for _ in range(2):
+        fleetshard.gather_bodies(body, dst=0, out=root_out)
+    barrier()
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 5
+    g0.record()
+    for _ in range(reps):
+        fleetshard.gather_bodies(body, dst=0, out=root_out)
+    g1.record()
+    barrier()
+    gms = fleetshard.max_over_ranks(g0.elapsed_time(g1) / reps, device=dev)
+    # ---- parity of what arrived (untimed)
+    if rank == 0:
+        root_out.fill_(0)
+    fleetshard.gather_bodies(body, dst=0, out=root_out)
+    sums = fleetshard.gather_checksums(body)
+    node_offs = [None] * world
+    dist.all_gather_object(node_offs, [int(x) for x in g.body_offsets()])
+    out = None
+    if rank == 0:
+        torch.cuda.synchronize()
+        checks_ok = fleetshard.verify_gather(root_out, offs, sums)
+        kgo = kgx_loader.load_oracle()  # the checker, outside every timed region
+        checked, oracle_ok = 0, True
+        if whole_body_oracle:
+            whole = Fleet.config(cfg)
+            o = kgo.Oracle(mode, kgo.JOIN_HASH, os.cpu_count() or 1)
+            o.set_table(whole.table(mode))
+            o.ingest(whole.scrape(0))
+            oracle_ok = root_out.cpu().numpy().tobytes() == o.render()
+            checked = n_total
+        else:
+            for r in range(world):
+                rlo, rhi = fleetshard.node_range(r, world, n_total)
+                for node in sorted({rlo, (rlo + rhi) // 2, rhi - 1})[:oracle_nodes]:
+                    sub = Fleet.config(cfg, n_nodes=1, node_base=node)
+                    o = kgo.Oracle(mode, kgo.JOIN_HASH, 1)
+                    o.set_table(sub.table(mode))
+                    o.ingest(sub.scrape(0))
+                    a = int(offs[r]) + node_offs[r][node - rlo]
+                    b = int(offs[r]) + node_offs[r][node - rlo + 1]
+                    oracle_ok = oracle_ok and root_out[a:b].cpu().numpy().tobytes() == o.render()
+                    checked += 1
+        inbound = int(offs[-1]) - int(lengths[0])
+        out = {"workload": "BASELINE.json configs[%d] split by node: %d nodes -> %s nodes per GPU" % (
+                   cfg - 1, n_total, "/".join(str(fleetshard.node_range(r, world, n_total)[1] - fleetshard.node_range(r, world, n_total)[0])
+                                              for r in sorted({0, world - 1}))),
+               "mode": {MODE_X: "X", 0: "R-intended", 1: "R-literal"}[mode], "samples_total": total_samples,
+               "ms_per_step": ms_max, "value": total_samples / (ms_max * 1e-3), "unit": UNIT, "gpu_launches_per_step": launches / steps,
+               "kernel_ms": {k: v[0] / max(1, steps) for k, v in prof.items()},
+               "gather": {"ms": gms, "bytes_on_root": int(offs[-1]), "inbound_bytes": inbound,
+                          "inbound_gbs": inbound / (gms * 1e-3) / 1e9 if gms > 0 else None,
+                          "frac_of_nvlink_inbound_900": inbound / (gms * 1e-3) / 1e9 / 900.0 if gms > 0 else None,
+                          "how": "lengths all-gather + one batched group of NCCL send/recv into rank 0's buffer, bodies in node order",
+                          "checksums_ok": bool(checks_ok), "oracle_ok": bool(oracle_ok),
+                          "oracle_checked": ("whole body" if whole_body_oracle else "%d nodes (first/middle/last of every rank)" % checked),
+                          "parity_ok": bool(checks_ok and oracle_ok)}}
+    g.close()
+    del keep
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -220,8 +402,8 @@ def main():
     ap.add_argument("--ref-nodes", type=int, default=100, help="nodes in the CPU sample")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--gather", action="store_true",
-                    help="N>1: also time the ordered concatenation of all bodies on rank 0 (NCCL send/recv over NVLink)")
+    ap.add_argument("--no-strong", action="store_true",
+                    help="N>1: skip the strong-scaling legs (split fleet, ordered gather on rank 0, parity check)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "kgx" else args.warmup
     if args.impl == "reference":
@@ -246,47 +428,18 @@ def main():
     g = kgx.Kgx(MODE_X, device=local, stream=stream.cuda_stream, profile=True)
     g.set_table(table)
 
-    # ---- inputs resident in HBM (torch owns the device buffers) ----------------
-    def dev_t(a):
-        return None if a is None else torch.from_numpy(a.view(np.int64) if a.dtype == np.uint64 else a.view(np.int32)).to(dev)
-
-    dcols = {k: dev_t(getattr(cols, k)) for k in ("pid", "gpu", "used", "node", "sm_util", "mem_util", "ts_us", "node_off", "gpu_total")}
-    ds = abi.kgx_cols()
-    ds.n = cols.n
-    for k, t in dcols.items():
-        if t is not None:
-            setattr(ds, k, C.cast(t.data_ptr(), abi.u64p if t.dtype == torch.int64 else abi.u32p))
-
-    def step_device():
-        g.reset_window()
-        g.ingest_device(ds)
-        return g.render_device()
+    ds, _keep = device_cols(cols, dev)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    with torch.cuda.stream(stream):
-        for _ in range(args.warmup):
-            body_len = step_device()
-        g.sync()
-        g.profile_reset()
-        launches0 = g.stats()["kernel_launches"]
-        clocks = ClockSampler(local)
-        clocks.start()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        barrier()
-        e0.record(stream)
-        for _ in range(args.steps):
-            body_len = step_device()
-        e1.record(stream)
-        barrier()
-        clk = clocks.stop()
-    ms = e0.elapsed_time(e1) / args.steps
+    clocks = ClockSampler(local)
+    ms, body_len, launches = timed_steps(g, ds, stream, args.steps, args.warmup, barrier, clocks=clocks)
+    clk = clocks.stop()
     prof = g.profile()
     st = g.stats()
-    launches = st["kernel_launches"] - launches0
     tmax = torch.tensor([ms], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -298,15 +451,15 @@ def main():
     peak, peak_src = peaks()
     n_fam = g.family_count()
     render_ms = prof["render"][0] / max(1, prof["render"][1])
-    ingest_ms = prof["ingest"][0] / max(1, prof["ingest"][1])
+    ingest_ms = prof["ingest"][0] / max(1, args.steps)  # join + its one-thread statistics hand-over
     series = st["n_series"]
     label_bytes = label_bytes_of(g, table, series)
     alg_render = n_fam * label_bytes + body_len
     achieved = alg_render / (render_ms * 1e-3) / 1e9 if render_ms > 0 else 0.0
     alg_pipeline = cols.n * 36 + len(table.entry_pid) * 12 + alg_render
-    roofline = {"bound": "hbm", "kernel": "k_render3<64> (exposition writer, kgx_writer.cuh)", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": ncu_traffic("r01_k_render3_raw.csv"), "peak_source": peak_src,
-                "traffic_source": "profiles/r01_k_render3_raw.csv (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, one launch)",
+    traffic, traffic_src = ncu_traffic(TRAFFIC_CSV, render_ms)
+    roofline = {"bound": "hbm", "kernel": "k_render5<128> (exposition writer, kgx_writer5.cuh)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src, "traffic_source": traffic_src,
                 "algorithmic_bytes_per_launch": alg_render, "kernel_ms": render_ms,
                 "share_of_step": render_ms / ms if ms else None,
                 "pipeline": {"algorithmic_bytes_per_step": alg_pipeline, "achieved_gbs": alg_pipeline / (ms * 1e-3) / 1e9,
@@ -368,31 +521,30 @@ def main():
         tm = torch.tensor([e_ms], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        floor_ms = copy_floor(dev, int(h2d), int(n_out), max(3, min(args.steps, 10)), barrier, world)
         e2e = {"value": total_samples / (float(tm.item()) * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(n_out), "ms_per_step": float(tm.item()), "host_memory": "pinned (kgx_host_alloc); " + numa_note.note,
-               "api": "kgx_reset_window + kgx_ingest + kgx_render_begin/kgx_render_end (body k-1 leaves while scrape k comes in)"}
+               "api": "kgx_reset_window + kgx_ingest + kgx_render_begin/kgx_render_end (body k-1 leaves while scrape k comes in)",
+               "copy_floor_ms": floor_ms, "frac_of_floor": floor_ms / float(tm.item()) if floor_ms else None,
+               "copy_floor": "bare copies of the same sizes in this process, no kernels: one pinned device->host copy of "
+                             "d2h_bytes_per_step per step with one pinned host->device copy of h2d_bytes_per_step running the "
+                             "other way on a second stream, all N ranks at once, max over ranks"}
 
-    # ---- optional: ordered concatenation of the per-GPU bodies on rank 0 ------------------
-    gather = None
-    if args.gather and world > 1:
-        from kgx_b200 import fleetshard
-        g.render_device()
-        ptr_, n_ = g.body_device()
-        local = torch.as_tensor(fleetshard.DeviceBytes(ptr_, n_), device=dev)
-        _, offs = fleetshard.gather_layout(n_, device=dev)
-        root_out = torch.empty(int(offs[-1]), dtype=torch.uint8, device=dev) if rank == 0 else None
-        for _ in range(2):
-            fleetshard.gather_bodies(local, dst=0, out=root_out)
-        barrier()
-        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        g0.record()
-        for _ in range(5):
-            fleetshard.gather_bodies(local, dst=0, out=root_out)
-        g1.record()
-        barrier()
-        gms = fleetshard.max_over_ranks(g0.elapsed_time(g1) / 5, device=dev)
-        gather = {"ms": gms, "bytes_on_root": int(offs[-1]), "inbound_gbs": (int(offs[-1]) - n_) / (gms * 1e-3) / 1e9 if rank == 0 else None,
-                  "how": "lengths all-gather + NCCL send/recv into rank 0's buffer, bodies stay in node order"}
+    # ---- N>1: the 10 M-sample fleet SPLIT over the ranks (strong scaling), gathered in order and byte-checked;
+    # and BASELINE config 3 (rack replay, 16 nodes per GPU at N=8) the same way ---------------------------------
+    strong = cfg3 = gather = None
+    if world > 1 and not args.no_strong:
+        g.close()  # the weak leg's context (several GB) is not needed any more
+        del _keep
+        strong = sharded_leg(CFG, MODE_X, rank, world, dev, local, args.steps, args.warmup, barrier)
+        cfg3 = sharded_leg(3, abi.MODE_R_INTENDED, rank, world, dev, local, args.steps, args.warmup, barrier, whole_body_oracle=True)
+        if rank == 0:
+            # the weak leg above IS the N=1 run of the same 10 M-sample fleet (every rank replays all 2 000 nodes)
+            strong["n1_ms_per_step"] = ms_max
+            strong["efficiency_vs_n1"] = ms_max / (world * strong["ms_per_step"])
+            strong["note"] = ("efficiency = (N=1 time of the whole fleet, this run's weak leg) / (N x time of the split fleet); "
+                              "kernel_ms vs ms_per_step shows the per-step host/launch share that does not shrink with the shard")
+            gather = strong.pop("gather")
 
     # ---- CPU baseline on this box's host cores (rank 0, N=1 only) --------------------
     cpu = None
@@ -407,7 +559,8 @@ def main():
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_max, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64/f64",
                 "data": "synthetic", "config": workload_config(args.nodes), "clocks": clk, "e2e": e2e,
-                "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "gather": gather,
+                "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "strong": strong, "gather": gather,
+                "cfg3_sharded": cfg3,
                 "series_per_gpu": int(series), "rendered_bytes_per_gpu": int(body_len),
                 "kernel_ms": {k: v[0] / max(1, args.steps) for k, v in prof.items()}}
         print(json.dumps(line), flush=True)
@@ -416,15 +569,10 @@ def main():
 
 
 def label_bytes_of(g, table, series):
-    """Pre-escaped label bytes of the live series (read once per family by the
-    render kernel): taken from the library's own slot texts."""
-    vals, slots = g.read_values(0, with_slots=True)
-    if len(slots) == 0:
-        return 0
-    if len(slots) > 20000:  # sample: label lengths are near-uniform in the synthetic fleet
-        idx = np.linspace(0, len(slots) - 1, 20000).astype(np.int64)
-        return int(np.mean([len(g.slot_labels(int(slots[i]))) for i in idx]) * len(slots))
-    return int(sum(len(g.slot_labels(int(s))) for s in slots))
+    """Pre-escaped label bytes of the live series (read once per family by the render kernel): exact, from the
+    library's bulk read-back of the label text (kgx_read_labels)."""
+    _, off = g.read_labels()
+    return int(off[-1])
 
 
 if __name__ == "__main__":

@@ -5,6 +5,7 @@
 package kgx
 
 import (
+	"fmt"
 	"net/http"
 	"strings"
 	"sync"
@@ -39,14 +40,26 @@ func (c *Collector) Describe(ch chan<- *prometheus.Desc) {
 // emits const metrics; used for protobuf/OpenMetrics scrapes.  Text scrapes
 // take the GPU-rendered body instead (Handler below).
 func (c *Collector) Collect(ch chan<- prometheus.Metric) {
-	for f, d := range c.descs {
-		vals, slots, err := c.ctx.ReadValues(f)
-		if err != nil {
+	// label text of all series in one call; entry i belongs to value i of every family
+	texts, err := c.ctx.ReadLabels()
+	if err != nil {
+		for _, d := range c.descs {
 			ch <- prometheus.NewInvalidMetric(d, err)
+		}
+		return
+	}
+	labels := make([][]string, len(texts))
+	for i, t := range texts {
+		labels[i] = labelValues(t)
+	}
+	for f, d := range c.descs {
+		vals, _, err := c.ctx.ReadValues(f)
+		if err != nil || len(vals) != len(labels) {
+			ch <- prometheus.NewInvalidMetric(d, fmt.Errorf("kgx read-back: %v (%d values, %d label sets)", err, len(vals), len(labels)))
 			continue
 		}
 		for i, v := range vals {
-			ch <- prometheus.MustNewConstMetric(d, prometheus.GaugeValue, v, labelValues(c.ctx.SlotLabels(slots[i]))...)
+			ch <- prometheus.MustNewConstMetric(d, prometheus.GaugeValue, v, labels[i]...)
 		}
 	}
 }

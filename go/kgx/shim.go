@@ -240,6 +240,26 @@ func (c *Ctx) ReadValues(family int) ([]float64, []uint32, error) {
 	return vals[:int(n)], slots[:int(n)], c.err(rc)
 }
 
+// ReadLabels returns the pre-escaped `{name="value",...}` text of every series that has a value, in exposition order
+// (entry i belongs to value i of every family), with one call into the library instead of one per series.
+func (c *Ctx) ReadLabels() ([]string, error) {
+	var n, nb C.size_t
+	if err := c.err(C.kgx_read_labels(c.p, nil, 0, nil, 0, &n, &nb)); err != nil {
+		return nil, err
+	}
+	blob := make([]byte, int(nb)+1)
+	off := make([]uint64, int(n)+1)
+	rc := C.kgx_read_labels(c.p, (*C.char)(unsafe.Pointer(&blob[0])), nb, u64p(off), C.size_t(len(off)), &n, &nb)
+	if err := c.err(rc); err != nil {
+		return nil, err
+	}
+	out := make([]string, int(n))
+	for i := range out {
+		out[i] = string(blob[off[i]:off[i+1]])
+	}
+	return out, nil
+}
+
 // SlotLabels returns the pre-escaped `{name="value",...}` text of a slot.
 func (c *Ctx) SlotLabels(slot uint32) string {
 	buf := make([]byte, 1024)

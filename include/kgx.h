@@ -186,7 +186,17 @@ int kgx_ingest(kgx_ctx* ctx, const kgx_cols* cols);
  * device memory): node_off, when given, has n_nodes+1 entries, starts at 0,
  * never decreases and ends at n.  Offsets beyond n make the join read past the
  * columns; rows outside [node_off[0], node_off[n_nodes]) are ignored.  When
- * both `node` and `node_off` are given, node_off decides the node of a row. */
+ * both `node` and `node_off` are given, node_off decides the node of a row.
+ * Unlike kgx_ingest, this call RETURNS WITH THE JOIN IN FLIGHT on ctx's stream:
+ * the caller's device columns must stay valid, and unmodified, until the next
+ * call on ctx that delivers results (kgx_render*, kgx_read_*, kgx_get_stats,
+ * kgx_sync, the next ingest ...).  That call also settles the batch: it reads
+ * the join's statistics and, if the batch brought series the index did not
+ * hold yet, rebuilds the index and folds what the first pass skipped (which
+ * allocates; call kgx_sync first if the next call must not, as
+ * kgx_render_noalloc).  A render queued behind an unsettled batch costs no
+ * extra host round trip: steady state is join kernel, writer kernel, one
+ * synchronisation. */
 int kgx_ingest_device(kgx_ctx* ctx, const kgx_cols* cols);
 
 /* R modes: ingest straight from what NVML hands back, without building columns
@@ -264,7 +274,7 @@ int kgx_render(kgx_ctx* ctx, uint8_t* out, size_t cap, size_t* len);
  * array takes KGX_NOALLOC_SCRATCH_BYTES on every GPU that loads the library,
  * for the life of the process.  It makes no cudaMalloc/cudaFree (nor any other
  * allocating call) and leaves the ctx-owned body of kgx_render untouched.
- *   - Limits: at most KGX_NOALLOC_MAX_TILES render tiles (a tile is up to 64
+ *   - Limits: at most KGX_NOALLOC_MAX_TILES render tiles (a tile is up to 128
  *     series of one family of one node) and KGX_NOALLOC_MAX_NODES nodes;
  *     beyond that it returns KGX_E_LIMIT and kgx_render must be used.
  *   - `cap` must cover the worst-case body size; if it does not (or d_out is

@@ -6,7 +6,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(CSRC, "libkgx.so")
 SOURCES = ["kgx_api.cu", "kgx_table.cpp"]
-DEPS = SOURCES + ["kgx_kernels.cuh", "kgx_writer.cuh", "kgx_build.cuh", "kgx_build_host.cuh", "kgx_async.cuh", "kgx_ingest2.cuh", "kgx_fmt.cuh", "kgx_table.hpp", "pow10_table.inc", os.path.join("..", "..", "include", "kgx.h")]
+DEPS = SOURCES + ["kgx_kernels.cuh", "kgx_writer.cuh", "kgx_writer5.cuh", "kgx_build.cuh", "kgx_build_host.cuh", "kgx_async.cuh", "kgx_ingest2.cuh", "kgx_fmt.cuh", "kgx_table.hpp", "pow10_table.inc", os.path.join("..", "..", "include", "kgx.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-Wall,-Wextra", "-shared", "-Xptxas", "-v"]
 

@@ -14,6 +14,7 @@
 #include "../../include/kgx.h"
 #include "kgx_kernels.cuh"
 #include "kgx_writer.cuh"
+#include "kgx_writer5.cuh"
 #include "kgx_ingest2.cuh"
 #include "kgx_table.hpp"
 #include "kgx_build.cuh"
@@ -70,7 +71,7 @@ struct kgx_ctx {
   uint64_t lbl_bytes = 0;
   std::vector<uint32_t> node_ser_off;
   // per-series state
-  DBuf d_acc[6];  // X: sum_used,max_used,last_ts,sum_sm,sum_mem,count ; R: r_seq,r_used,r_total
+  DBuf d_acc[6];  // X: [0] = xa, [1] = xb records per series (kgx_kernels.cuh) ; R: r_seq,r_used,r_total
   DBuf d_acc_spare[6];  // target of the next index rebuild
   DBuf d_node_live, d_gpu_total;
   bool have_total = false;
@@ -78,6 +79,7 @@ struct kgx_ctx {
   DBuf d_fam, d_tiles, d_tile_state, d_node_body_off, d_out, d_out_alt;
   uint32_t n_tiles = 0, tile_lines = 0, render_smem = 0;
   bool render_v2 = false;  // second-generation writer (needs metric names of 15..64 bytes)
+  int writer_gen = 5;      // 5: k_render5 (two tiles in flight per CTA, the default); 3: k_render3 (one tile at a time)
   RenderLayout lay{};
   int render_grid = 0, render_threads = 64;   // measured best on B200: direct stores, 64-line tiles
   size_t last_len = 0;
@@ -92,12 +94,22 @@ struct kgx_ctx {
   DBuf d_cols[8];
   DBuf d_tmp[6];
   uint32_t seq = 0;
+  // kgx_ingest_device returns once its kernels are queued: the statistics and the churn check of that join are
+  // settled by the next call that needs them (settle_ingest), or ride on the writer's own synchronisation
+  bool reset_pending = false;  // X: kgx_reset_window was called; the next node-grouped join clears as it goes (else flush_reset)
+  bool ingest_pending = false;
+  kgx::DevCols pending_cols{};
+  bool pending_grouped = false;
+  uint32_t render_epoch = 0, body_epoch = 0;  // tag of the look-back words / body offsets of the latest launch
   kgx_stats stats{};
   kgx_profile prof{};
   std::vector<TimedRegion> regions;
 };
 
 namespace {
+
+constexpr int kCounterWords = 16;  // C_COUNT words the kernels know + two scratch words for kgx_expire
+constexpr int kExpireWords = 8;
 
 const char* const kErrNames[] = {"ok", "invalid argument", "out of memory", "CUDA error", "output buffer too small",
                                  "call out of order", "size beyond a documented maximum"};
@@ -186,9 +198,7 @@ int device_scan(kgx_ctx* c, const uint32_t* in, uint64_t n, unsigned long long* 
 DevAcc acc_view(kgx_ctx* c) {
   DevAcc a{};
   if (c->mode == KGX_MODE_X) {
-    a.sum_used = ptr<unsigned long long>(c->d_acc[0]); a.max_used = ptr<unsigned long long>(c->d_acc[1]);
-    a.last_ts = ptr<unsigned long long>(c->d_acc[2]); a.sum_sm = ptr<unsigned long long>(c->d_acc[3]);
-    a.sum_mem = ptr<unsigned long long>(c->d_acc[4]); a.count = ptr<unsigned long long>(c->d_acc[5]);
+    a.xa = ptr<unsigned long long>(c->d_acc[0]); a.xb = ptr<unsigned long long>(c->d_acc[1]);
   } else {
     a.r_seq = ptr<unsigned long long>(c->d_acc[0]); a.r_used = ptr<unsigned long long>(c->d_acc[1]);
     a.r_total = ptr<unsigned long long>(c->d_acc[2]);
@@ -196,10 +206,17 @@ DevAcc acc_view(kgx_ctx* c) {
   a.node_live = ptr<uint32_t>(c->d_node_live);
   return a;
 }
-int n_acc_arrays(const kgx_ctx* c) { return c->mode == KGX_MODE_X ? 6 : 3; }
+int n_acc_arrays(const kgx_ctx* c) { return c->mode == KGX_MODE_X ? 2 : 3; }  // X: xa, xb (kgx_kernels.cuh)
+int acc_words(const kgx_ctx* c, int k) { return c->mode == KGX_MODE_X ? (k == 0 ? int(kXAWords) : int(kXBWords)) : 1; }  // words per series
 
 // the writer is compiled for four CTA sizes (= lines per tile); 64 measured best on B200
 const void* writer_func(const kgx_ctx* c) {
+  if (c->writer_gen == 5) switch (c->render_threads) {
+    case 32: return reinterpret_cast<const void*>(&k_render5<32>);
+    case 128: return reinterpret_cast<const void*>(&k_render5<128>);
+    case 256: return reinterpret_cast<const void*>(&k_render5<256>);
+    default: return reinterpret_cast<const void*>(&k_render5<64>);
+  }
   switch (c->render_threads) {
     case 32: return reinterpret_cast<const void*>(&k_render3<32>);
     case 128: return reinterpret_cast<const void*>(&k_render3<128>);
@@ -208,6 +225,15 @@ const void* writer_func(const kgx_ctx* c) {
   }
 }
 void launch_writer(kgx_ctx* c, int grid, const DevRender& R, unsigned long long* counters) {
+  if (c->writer_gen == 5) {
+    switch (c->render_threads) {
+      case 32: k_render5<32><<<grid, 32, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+      case 128: k_render5<128><<<grid, 128, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+      case 256: k_render5<256><<<grid, 256, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+      default: k_render5<64><<<grid, 64, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+    }
+    return;
+  }
   switch (c->render_threads) {
     case 32: k_render3<32><<<grid, 32, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
     case 128: k_render3<128><<<grid, 128, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
@@ -263,8 +289,8 @@ int rebuild_index(kgx_ctx* c) {
   const int na = n_acc_arrays(c);
   DBuf* new_acc = c->d_acc_spare;  // the two sets swap roles at every rebuild: no allocation in steady churn
   for (int k = 0; k < na; ++k) {
-    KGX_TRY(dev_reserve(c, new_acc[k], size_t(S) * 8));
-    KGX_CUDA(c, cudaMemsetAsync(new_acc[k].p, 0, size_t(S) * 8, c->stream));
+    KGX_TRY(dev_reserve(c, new_acc[k], size_t(S) * 8 * acc_words(c, k)));
+    KGX_CUDA(c, cudaMemsetAsync(new_acc[k].p, 0, size_t(S) * 8 * acc_words(c, k), c->stream));
   }
   if (old_n) {
     const unsigned long long* h_old[6]; unsigned long long* h_new[6];
@@ -272,9 +298,10 @@ int rebuild_index(kgx_ctx* c) {
     KGX_TRY(dev_reserve(c, c->d_tmp[0], 2 * 6 * sizeof(void*)));
     KGX_CUDA(c, cudaMemcpyAsync(c->d_tmp[0].p, h_old, sizeof h_old, cudaMemcpyHostToDevice, c->stream));
     KGX_CUDA(c, cudaMemcpyAsync(static_cast<char*>(c->d_tmp[0].p) + sizeof h_old, h_new, sizeof h_new, cudaMemcpyHostToDevice, c->stream));
-    k_remap<<<cdiv(old_n, 256), 256, 0, c->stream>>>(ptr<uint32_t>(c->d_ser_slot), old_n, ptr<uint2>(c->d_bm), na,
-                                                     reinterpret_cast<const unsigned long long* const*>(c->d_tmp[0].p),
-                                                     reinterpret_cast<unsigned long long* const*>(static_cast<char*>(c->d_tmp[0].p) + sizeof h_old));
+    for (int k = 0; k < na; ++k)  // one launch per array: their records differ in size
+      k_remap<<<cdiv(old_n, 256), 256, 0, c->stream>>>(ptr<uint32_t>(c->d_ser_slot), old_n, ptr<uint2>(c->d_bm), 1, acc_words(c, k),
+                                                       reinterpret_cast<const unsigned long long* const*>(c->d_tmp[0].p) + k,
+                                                       reinterpret_cast<unsigned long long* const*>(static_cast<char*>(c->d_tmp[0].p) + sizeof h_old) + k);
     tm.launches(1);
     KGX_CUDA(c, cudaStreamSynchronize(c->stream));  // h_old/h_new are stack arrays
   }
@@ -331,6 +358,10 @@ int rebuild_index(kgx_ctx* c) {
     tm.launches(1);
   }
   KGX_TRY(dev_reserve(c, c->d_tile_state, size_t(c->n_tiles) * 8 + 8));
+  KGX_CUDA(c, cudaMemsetAsync(c->d_tile_state.p, 0, c->d_tile_state.cap, c->stream));  // (re)allocated: no stale epoch tags
+  KGX_CUDA(c, cudaMemsetAsync(c->d_node_body_off.p, 0xff, c->d_node_body_off.cap, c->stream));
+  KGX_CUDA(c, cudaMemsetAsync(ptr<unsigned long long>(c->d_counters) + C_TICKET, 0, 16, c->stream));  // both tickets
+  c->render_epoch = 0;
   // R modes: every series has a value, so a node is live iff it has series
   if (c->mode != KGX_MODE_X) {
     std::vector<uint32_t> live(NN);
@@ -418,6 +449,24 @@ int upload_plan(kgx_ctx* c) {
   return KGX_OK;
 }
 
+// The dynamic shared-memory limit is an attribute of the FUNCTION (per device), shared by every ctx in the process: it is
+// only ever raised, or a ctx with a small table would pull it below what another ctx's launches need.
+int raise_smem_limit(kgx_ctx* c, const void* fn, uint32_t bytes) {
+  static std::mutex mu;
+  static std::vector<std::pair<std::pair<int, const void*>, uint32_t>> seen;
+  std::lock_guard<std::mutex> g(mu);
+  for (auto& e : seen)
+    if (e.first.first == c->device && e.first.second == fn) {
+      if (bytes <= e.second) return KGX_OK;
+      KGX_CUDA(c, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes)));
+      e.second = bytes;
+      return KGX_OK;
+    }
+  KGX_CUDA(c, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes)));
+  seen.push_back({{c->device, fn}, bytes});
+  return KGX_OK;
+}
+
 // Everything that depends on the table only through its sizes (plan.n_slots, n_nodes, G, max_*; ctx.max_words):
 // the join's staging buffer, the series index, the render tile geometry.  Shared by the host and the device build.
 int finish_plan(kgx_ctx* c) {
@@ -431,7 +480,7 @@ int finish_plan(kgx_ctx* c) {
     c->ingest_smem = uint32_t(uint64_t(c->ingest_cells) * sizeof(Entry) + uint64_t(c->ingest_pks) * 8 + uint64_t(c->ingest_words) * 8 + 16);
     const void* fns[] = {(const void*)&k_ingest_nodes<true, 0>, (const void*)&k_ingest_nodes<true, 1>,
                          (const void*)&k_ingest_nodes<false, 0>, (const void*)&k_ingest_nodes<false, 1>};
-    for (const void* f : fns) KGX_CUDA(c, cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->ingest_smem)));
+    for (const void* f : fns) KGX_TRY(raise_smem_limit(c, f, c->ingest_smem));
   }
   c->n_words = cdiv(p.n_slots, 32) + 1;
   KGX_TRY(dev_reserve(c, c->d_bm, size_t(c->n_words) * 8));
@@ -455,26 +504,31 @@ int finish_plan(kgx_ctx* c) {
   int occ = 1;
   if (c->render_v2) {
     // per line: value slot + staged label.  Small CTAs: many independent tiles per SM hide each other's latencies
+    if (const char* e = getenv("KGX_WRITER")) c->writer_gen = atoi(e) == 3 ? 3 : 5;
+    // lines per tile = threads per CTA; measured best on B200: 128 for the pipelined writer, 64 for k_render3
+    c->render_threads = c->writer_gen == 5 ? 128 : 64;
     if (const char* e = getenv("KGX_RENDER_THREADS")) c->render_threads = atoi(e);
-    if (c->render_threads != 32 && c->render_threads != 128 && c->render_threads != 256) c->render_threads = 64;
-    const uint64_t fixed = uint64_t(kMaxFamilies) * kNameStride + uint64_t(c->render_threads) * kSlotBytes + 32 + (32 + 128 + 48) + 32;
+    if (c->render_threads != 32 && c->render_threads != 64 && c->render_threads != 128 && c->render_threads != 256)
+      c->render_threads = c->writer_gen == 5 ? 128 : 64;
+    const uint64_t slot_bufs = c->writer_gen == 5 ? 2 : 1;
+    const uint64_t fixed = uint64_t(kMaxFamilies) * kNameStride + slot_bufs * c->render_threads * kSlotBytes + 32 + (32 + 128 + 48) + 32;
     uint64_t budget = 200 * 1024;
     if (fixed + p.max_label_len > budget) return fail(c, KGX_E_LIMIT, "label text too long for one render tile");
     c->tile_lines = uint32_t(std::min<uint64_t>(uint64_t(c->render_threads), (budget - fixed) / std::max<uint64_t>(1, p.max_label_len)));
     auto up16 = [](uint64_t v) { return uint32_t((v + 15) & ~15ull); };
     c->lay.names = 0;
     c->lay.slots = up16(uint64_t(kMaxFamilies) * kNameStride);
-    c->lay.stage = up16(c->lay.slots + uint64_t(c->render_threads) * kSlotBytes + 32);
+    c->lay.stage = up16(c->lay.slots + slot_bufs * c->render_threads * kSlotBytes + 32);
     c->lay.total = up16(c->lay.stage + 32 + uint64_t(c->tile_lines) * p.max_label_len + 128 + 48);
     c->render_smem = c->lay.total;
-    KGX_CUDA(c, cudaFuncSetAttribute(writer_func(c), cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->render_smem)));
+    KGX_TRY(raise_smem_limit(c, writer_func(c), c->render_smem));
     KGX_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, writer_func(c), c->render_threads, c->render_smem));
   } else {
     const uint64_t budget = 96 * 1024;
     if (max_line + max_header + 32 > budget) return fail(c, KGX_E_LIMIT, "label text too long for one render tile");
     c->tile_lines = uint32_t(std::min<uint64_t>(kRenderThreads, (budget - max_header - 32) / max_line));
     c->render_smem = uint32_t((max_header + uint64_t(c->tile_lines) * max_line + 32 + 15) & ~15ull);
-    KGX_CUDA(c, cudaFuncSetAttribute(k_render, cudaFuncAttributeMaxDynamicSharedMemorySize, int(c->render_smem)));
+    KGX_TRY(raise_smem_limit(c, reinterpret_cast<const void*>(&k_render), c->render_smem));
     KGX_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_render, kRenderThreads, c->render_smem));
   }
   c->render_grid = std::max(1, occ) * c->sm_count;
@@ -525,6 +579,99 @@ int set_table_device(kgx_ctx* c, const kgx_table* t, CarriedDev* carried) {
   return KGX_OK;
 }
 
+// Launch one pass of the join over the batch `dc` (PASS 0: steady state; PASS 1: after an index rebuild, folds exactly
+// the matches pass 0 had to skip).
+// A pending window reset, carried out on its own (the next call is not a node-grouped join that could fold it in).
+int flush_reset(kgx_ctx* c) {
+  if (!c->reset_pending) return KGX_OK;
+  c->reset_pending = false;
+  if (!c->have_table || c->mode != KGX_MODE_X) return KGX_OK;
+  Timed tm(c, KGX_K_OTHER);
+  const uint32_t items = std::max<uint32_t>(c->n_series, c->plan.n_nodes);
+  const uint32_t grid = std::max(1u, std::min<uint32_t>(cdiv(items, 256), uint32_t(c->sm_count) * 8));
+  k_clear_window<<<grid, 256, 0, c->stream>>>(acc_view(c), c->n_series, c->plan.n_nodes);
+  tm.launches(1);
+  return launch_check(c, "k_clear_window");
+}
+
+// CTAs that share one node's rows in the node-grouped join: 1 for a fleet; a lone busy node is split (about 2 K rows each)
+uint32_t ingest_parts(const kgx_ctx* c, uint64_t n_rows) {
+  const uint32_t ctas = uint32_t(c->sm_count) * 2;
+  if (c->plan.n_nodes >= ctas) return 1;
+  const uint64_t by_rows = std::max<uint64_t>(1, n_rows / std::max<uint32_t>(1, c->plan.n_nodes) / 2048);
+  return uint32_t(std::min<uint64_t>(std::min<uint64_t>(by_rows, ctas / c->plan.n_nodes), 64));
+}
+
+void launch_ingest_pass(kgx_ctx* c, const DevCols& dc, bool grouped, int pass, bool reset = false) {
+  const Plan& p = c->plan;
+  const bool x = c->mode == KGX_MODE_X;
+  unsigned long long* ctr = ptr<unsigned long long>(c->d_counters);
+  DevTable t{ptr<NodeTab>(c->d_node_tab), ptr<Entry>(c->d_tab), ptr<uint32_t>(c->d_pk_slot0), ptr<uint32_t>(c->d_pk_stride),
+             ptr<uint32_t>(c->d_grank), p.n_nodes, p.G};
+  DevIndex ix{ptr<uint2>(c->d_bm), ptr<uint32_t>(c->d_pending), c->n_words};
+  const int grid = int(std::min<uint64_t>(uint64_t(c->sm_count) * 8, std::max<uint64_t>(1, cdiv(dc.n, 256))));
+  const DevNodeMeta nm{ptr<uint32_t>(c->d_node_a_base), c->ingest_cells, c->ingest_pks, ptr<uint32_t>(c->d_node_slot_base), c->ingest_words,
+                       ptr<uint32_t>(c->d_node_ser_off), reset ? 1u : 0u, ingest_parts(c, dc.n)};
+  const int ngrid = int(std::min<uint32_t>(p.n_nodes * nm.parts, uint32_t(c->sm_count) * 2));
+  if (grouped) {  // rows grouped by node: one CTA per node, table slice staged in shared memory
+    if (x && pass == 0) k_ingest_nodes<true, 0><<<ngrid, kIngestThreads, c->ingest_smem, c->stream>>>(t, nm, ix, acc_view(c), dc, c->seq, ctr);
+    else if (x) k_ingest_nodes<true, 1><<<ngrid, kIngestThreads, c->ingest_smem, c->stream>>>(t, nm, ix, acc_view(c), dc, c->seq, ctr);
+    else if (pass == 0) k_ingest_nodes<false, 0><<<ngrid, kIngestThreads, c->ingest_smem, c->stream>>>(t, nm, ix, acc_view(c), dc, c->seq, ctr);
+    else k_ingest_nodes<false, 1><<<ngrid, kIngestThreads, c->ingest_smem, c->stream>>>(t, nm, ix, acc_view(c), dc, c->seq, ctr);
+  } else {
+    if (x && pass == 0) k_ingest<true, 0><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
+    else if (x) k_ingest<true, 1><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
+    else if (pass == 0) k_ingest<false, 0><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
+    else k_ingest<false, 1><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
+  }
+}
+
+// `with_epilogue`: the launch also hands the join's statistics over; returns false in *did if nothing was launched
+int launch_finalize_r(kgx_ctx* c, const DevCols& dc, bool grouped, bool with_epilogue = false, bool* did = nullptr) {
+  if (did) *did = false;
+  if (c->mode == KGX_MODE_X || !c->n_series || !dc.n) return KGX_OK;
+  if (did) *did = true;
+  Timed tm(c, KGX_K_FINALIZE);
+  DevCols fc = dc;
+  if (grouped) fc.node = nullptr;  // the node of a row is derived the way the join derived it: from node_off
+  k_finalize_r<<<cdiv(c->n_series, 256), 256, 0, c->stream>>>(acc_view(c), fc, ptr<unsigned long long>(c->d_gpu_total), c->plan.G,
+                                                              c->seq, c->n_series, c->plan.n_nodes,
+                                                              with_epilogue ? ptr<unsigned long long>(c->d_counters) : nullptr, c->h_counters_dev);
+  tm.launches(1);
+  return launch_check(c, "k_finalize_r");
+}
+
+// The join of the pending batch saw series the index does not hold: merge them in, fold what pass 0 skipped.
+int handle_churn(kgx_ctx* c) {
+  KGX_TRY(rebuild_index(c));
+  {
+    Timed tm(c, KGX_K_INGEST);
+    launch_ingest_pass(c, c->pending_cols, c->pending_grouped, 1);
+    tm.launches(1);
+    KGX_TRY(launch_check(c, "k_ingest churn pass"));
+  }
+  KGX_CUDA(c, cudaMemsetAsync(c->d_pending.p, 0, size_t(c->n_words) * 4, c->stream));
+  KGX_CUDA(c, cudaMemsetAsync(ptr<unsigned long long>(c->d_counters) + C_CHURN, 0, 8, c->stream));
+  return launch_finalize_r(c, c->pending_cols, c->pending_grouped);
+}
+
+// Statistics and churn check of the latest join (queued by ingest_device_locked): wait for it, read what its last
+// CTA posted to mapped host memory, and run the churn path if it saw new series.
+int settle_ingest(kgx_ctx* c) {
+  if (!c->ingest_pending) return KGX_OK;
+  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->ingest_pending = false;
+  c->stats.n_matched = c->h_counters[C_MATCHED];
+  c->stats.n_dropped = c->h_counters[C_DROPPED];
+  if (c->h_counters[C_NEW]) {
+    KGX_TRY(handle_churn(c));
+    KGX_CUDA(c, cudaStreamSynchronize(c->stream));  // the caller's device columns may go away after this call
+  }
+  return KGX_OK;
+}
+
+// Queue the join + reduce of one batch whose columns are device memory.  Returns with the work in flight
+// (c->ingest_pending); settle_ingest() or the next render completes it.
 int ingest_device_locked(kgx_ctx* c, const kgx_cols* s) {
   if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_ingest before kgx_set_table");
   if (!s->gpu_total) return fail(c, KGX_E_INVAL, "cols: gpu_total missing");
@@ -532,85 +679,52 @@ int ingest_device_locked(kgx_ctx* c, const kgx_cols* s) {
   const bool x = c->mode == KGX_MODE_X;
   if (x && s->n && (!s->sm_util || !s->mem_util || !s->ts_us)) return fail(c, KGX_E_INVAL, "cols: X mode needs sm_util, mem_util, ts_us");
   if (s->n >= 0xffffffffull) return fail(c, KGX_E_LIMIT, "more than 2^32-1 samples in one ingest");
+  KGX_TRY(settle_ingest(c));  // one batch in flight at a time: its churn pass needs its columns
   const Plan& p = c->plan;
   KGX_CUDA(c, cudaMemcpyAsync(c->d_gpu_total.p, s->gpu_total, size_t(p.n_nodes) * p.G * 8, cudaMemcpyDefault, c->stream));
   c->have_total = true;
   c->seq += 1;
   c->rendered = false;
-  unsigned long long* ctr = ptr<unsigned long long>(c->d_counters);
-  KGX_CUDA(c, cudaMemsetAsync(ctr, 0, 3 * 8, c->stream));
-  DevTable t{ptr<NodeTab>(c->d_node_tab), ptr<Entry>(c->d_tab), ptr<uint32_t>(c->d_pk_slot0), ptr<uint32_t>(c->d_pk_stride),
-             ptr<uint32_t>(c->d_grank), p.n_nodes, p.G};
-  DevIndex ix{ptr<uint2>(c->d_bm), ptr<uint32_t>(c->d_pending), c->n_words};
-  DevCols dc{s->pid, s->gpu, s->node, s->sm_util, s->mem_util, reinterpret_cast<const unsigned long long*>(s->used),
-             reinterpret_cast<const unsigned long long*>(s->ts_us), reinterpret_cast<const unsigned long long*>(s->node_off), s->n};
-  const int grid = int(std::min<uint64_t>(uint64_t(c->sm_count) * 8, std::max<uint64_t>(1, cdiv(s->n, 256))));
-  // rows grouped by node: one CTA per node, table slice staged in shared memory
+  const DevCols dc{s->pid, s->gpu, s->node, s->sm_util, s->mem_util, reinterpret_cast<const unsigned long long*>(s->used),
+                   reinterpret_cast<const unsigned long long*>(s->ts_us), reinterpret_cast<const unsigned long long*>(s->node_off), s->n};
   const bool grouped = s->node_off != nullptr && !getenv("KGX_INGEST_V1");
-  const DevNodeMeta nm{ptr<uint32_t>(c->d_node_a_base), c->ingest_cells, c->ingest_pks, ptr<uint32_t>(c->d_node_slot_base), c->ingest_words};
-  const int ngrid = int(std::min<uint32_t>(p.n_nodes, uint32_t(c->sm_count) * 2));
-  auto launch_ingest = [&](int pass) {
-    if (grouped) {
-      if (x && pass == 0) k_ingest_nodes<true, 0><<<ngrid, kIngestThreads, c->ingest_smem, c->stream>>>(t, nm, ix, acc_view(c), dc, c->seq, ctr);
-      else if (x) k_ingest_nodes<true, 1><<<ngrid, kIngestThreads, c->ingest_smem, c->stream>>>(t, nm, ix, acc_view(c), dc, c->seq, ctr);
-      else if (pass == 0) k_ingest_nodes<false, 0><<<ngrid, kIngestThreads, c->ingest_smem, c->stream>>>(t, nm, ix, acc_view(c), dc, c->seq, ctr);
-      else k_ingest_nodes<false, 1><<<ngrid, kIngestThreads, c->ingest_smem, c->stream>>>(t, nm, ix, acc_view(c), dc, c->seq, ctr);
-    } else {
-      if (x && pass == 0) k_ingest<true, 0><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
-      else if (x) k_ingest<true, 1><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
-      else if (pass == 0) k_ingest<false, 0><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
-      else k_ingest<false, 1><<<grid, 256, 0, c->stream>>>(t, ix, acc_view(c), dc, c->seq, ctr);
-    }
-  };
-  if (s->n) {
+  {
     Timed tm(c, KGX_K_INGEST);
-    launch_ingest(0);
+    // the statistics reach mapped host memory by a store of the kernel's last CTA, not by a D2H copy: a copy would
+    // queue on the device->host copy engine behind a body that kgx_render_begin may still be sending (tens of ms)
+    // the join clears each node as it takes it — if one CTA owns the node
+    const bool fold_reset = c->reset_pending && x && grouped && s->n && c->n_series && ingest_parts(c, s->n) == 1;
+    if (!fold_reset) KGX_TRY(flush_reset(c));
+    c->reset_pending = false;
+    if (s->n) launch_ingest_pass(c, dc, grouped, 0, fold_reset);
+    else k_ingest_nothing<<<1, 32, 0, c->stream>>>(ptr<unsigned long long>(c->d_counters), c->h_counters_dev);
     tm.launches(1);
     KGX_TRY(launch_check(c, "k_ingest"));
   }
-  // the statistics go to mapped host memory by a store, not by a D2H copy: a copy would queue on the device->host
-  // copy engine behind a body that kgx_render_begin may still be sending (tens of ms)
-  k_post_words<<<1, 32, 0, c->stream>>>(ctr, c->h_counters_dev, 3);
-  c->stats.kernel_launches += 1;
-  KGX_CUDA(c, cudaStreamSynchronize(c->stream));
-  c->stats.n_matched = c->h_counters[C_MATCHED];
-  c->stats.n_dropped = c->h_counters[C_DROPPED];
-  if (c->h_counters[C_NEW]) {  // churn: series seen for the first time
-    KGX_TRY(rebuild_index(c));
-    {
-      Timed tm(c, KGX_K_INGEST);
-      launch_ingest(1);
-      tm.launches(1);
-      KGX_TRY(launch_check(c, "k_ingest churn pass"));
-    }
-    KGX_CUDA(c, cudaMemsetAsync(c->d_pending.p, 0, size_t(c->n_words) * 4, c->stream));
-  }
-  if (!x && c->n_series && s->n) {
-    Timed tm(c, KGX_K_FINALIZE);
-    DevCols fc = dc;
-    if (grouped) fc.node = nullptr;  // the node of a row is derived the way the join derived it: from node_off
-    k_finalize_r<<<cdiv(c->n_series, 256), 256, 0, c->stream>>>(acc_view(c), fc, ptr<unsigned long long>(c->d_gpu_total), p.G,
-                                                                c->seq, c->n_series, p.n_nodes);
+  bool handed_over = false;  // R modes: k_finalize_r posts the statistics too
+  KGX_TRY(launch_finalize_r(c, dc, grouped, true, &handed_over));
+  if (s->n && !handed_over) {
+    Timed tm(c, KGX_K_INGEST);
+    k_ingest_epilogue<<<1, 32, 0, c->stream>>>(ptr<unsigned long long>(c->d_counters), c->h_counters_dev);
     tm.launches(1);
-    KGX_TRY(launch_check(c, "k_finalize_r"));
+    KGX_TRY(launch_check(c, "k_ingest_epilogue"));
   }
+  c->pending_cols = dc;
+  c->pending_grouped = grouped;
+  c->ingest_pending = true;
   return KGX_OK;
 }
 
-int render_device_locked(kgx_ctx* c, size_t* len, bool keep_copies = false) {
-  if (!keep_copies) wait_copy(c);
-  // a scrape may arrive before the first poll cycle (the reference starts its HTTP server first, main.go:68-74):
-  // an empty registry gathers nothing, so the body is empty
-  c->body_off_valid = false;
-  if (!c->have_table) { c->last_len = 0; c->rendered = true; if (len) *len = 0; return KGX_OK; }
-  if (c->n_tiles == 0) { c->last_len = 0; c->rendered = true; if (len) *len = 0; c->stats.rendered_bytes = 0; return KGX_OK; }
+int launch_render(kgx_ctx* c, uint8_t* out, bool guard) {
   unsigned long long* ctr = ptr<unsigned long long>(c->d_counters);
-  {
-    Timed tm(c, KGX_K_OTHER);
-    KGX_CUDA(c, cudaMemsetAsync(ctr + C_TOTAL_LEN, 0, 2 * 8, c->stream));
-    KGX_CUDA(c, cudaMemsetAsync(c->d_tile_state.p, 0, size_t(c->n_tiles) * 8, c->stream));
-    KGX_CUDA(c, cudaMemsetAsync(c->d_node_body_off.p, 0xff, (size_t(c->plan.n_nodes) + 1) * 8, c->stream));
+  if (c->render_epoch >= kStEpochMax) {  // the 14-bit epoch tag wraps: clear the tagged arrays once, start over
+    KGX_CUDA(c, cudaMemsetAsync(c->d_tile_state.p, 0, c->d_tile_state.cap, c->stream));
+    KGX_CUDA(c, cudaMemsetAsync(c->d_node_body_off.p, 0xff, c->d_node_body_off.cap, c->stream));
+    KGX_CUDA(c, cudaMemsetAsync(ptr<unsigned long long>(c->d_counters) + C_TICKET, 0, 16, c->stream));
+    c->render_epoch = 0;
   }
+  c->render_epoch += 1;
+  c->body_epoch = c->render_epoch;
   DevRender R{};
   R.fam = ptr<FamMeta>(c->d_fam); R.n_families = uint32_t(c->fam.size());
   R.tiles = ptr<Tile>(c->d_tiles); R.n_tiles = c->n_tiles;
@@ -618,21 +732,43 @@ int render_device_locked(kgx_ctx* c, size_t* len, bool keep_copies = false) {
   R.ser_len = ptr<uint32_t>(c->d_ser_len);
   R.ser_gidx = ptr<uint32_t>(c->d_ser_gidx); R.gpu_total = ptr<unsigned long long>(c->d_gpu_total);
   R.tile_state = ptr<unsigned long long>(c->d_tile_state); R.node_body_off = ptr<unsigned long long>(c->d_node_body_off);
-  R.out = ptr<uint8_t>(c->d_out); R.smem_bytes = c->render_smem;
-  {
-    Timed tm(c, KGX_K_RENDER);
-    const int grid = int(std::min<uint32_t>(c->n_tiles, uint32_t(c->render_grid)));
-    if (c->render_v2) launch_writer(c, grid, R, ctr);
-    else k_render<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, acc_view(c), ctr);
-    tm.launches(1);
-    KGX_TRY(launch_check(c, "k_render"));
-  }
-  k_post_words<<<1, 32, 0, c->stream>>>(ctr + C_TOTAL_LEN, c->h_counters_dev + C_TOTAL_LEN, 1);  // see ingest_device_locked
-  c->stats.kernel_launches += 1;
+  R.out = out; R.smem_bytes = c->render_smem;
+  R.epoch = c->render_epoch; R.check_churn = guard ? 1u : 0u; R.host_len = c->h_counters_dev + C_TOTAL_LEN;
+  Timed tm(c, KGX_K_RENDER);
+  const int grid = int(std::min<uint32_t>(c->n_tiles, uint32_t(c->render_grid)));
+  if (c->render_v2) launch_writer(c, grid, R, ctr);
+  else k_render<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, acc_view(c), ctr);
+  tm.launches(1);
+  return launch_check(c, "k_render");
+}
+
+int render_device_locked(kgx_ctx* c, size_t* len, bool keep_copies = false) {
+  if (!keep_copies) wait_copy(c);
+  c->body_off_valid = false;
+  // a scrape may arrive before the first poll cycle (the reference starts its HTTP server first, main.go:68-74):
+  // an empty registry gathers nothing, so the body is empty
+  if (!c->have_table) { c->last_len = 0; c->rendered = true; if (len) *len = 0; return KGX_OK; }
+  KGX_TRY(flush_reset(c));  // (no-op unless kgx_reset_window was the last call)
+  if (c->n_tiles == 0) KGX_TRY(settle_ingest(c));  // a first batch may bring the first series
+  if (c->n_tiles == 0) { c->last_len = 0; c->rendered = true; if (len) *len = 0; c->stats.rendered_bytes = 0; return KGX_OK; }
+  // A join may still be in flight (kgx_ingest_device).  The writer is queued behind it without a host round trip and
+  // checks on the device that the join met no new series; if it did, the writer leaves at once and the churn path
+  // runs here before a second launch.  Steady state: two kernels, one synchronisation.
+  const bool guard = c->ingest_pending;
+  KGX_TRY(launch_render(c, ptr<uint8_t>(c->d_out), guard));
   KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (guard) {
+    c->ingest_pending = false;
+    c->stats.n_matched = c->h_counters[C_MATCHED];
+    c->stats.n_dropped = c->h_counters[C_DROPPED];
+    if (c->h_counters[C_NEW]) {
+      KGX_TRY(handle_churn(c));
+      KGX_TRY(launch_render(c, ptr<uint8_t>(c->d_out), false));
+      KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+  }
   c->last_len = size_t(c->h_counters[C_TOTAL_LEN]);
   c->rendered = true;
-  c->body_off_valid = false;
   c->stats.rendered_bytes = c->last_len;
   if (len) *len = c->last_len;
   return KGX_OK;
@@ -647,8 +783,10 @@ int fetch_body_offsets(kgx_ctx* c) {
     KGX_CUDA(c, cudaMemcpyAsync(c->body_off.data(), c->d_node_body_off.p, (NN + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
     KGX_CUDA(c, cudaStreamSynchronize(c->stream));
     c->body_off[NN] = c->last_len;
-    for (size_t k = NN; k-- > 0;)  // nodes without series have an empty body
-      if (c->body_off[k] == ~0ull) c->body_off[k] = c->body_off[k + 1];
+    for (size_t k = NN; k-- > 0;) {  // an entry counts if the latest launch wrote it; nodes without series have an empty body
+      const uint64_t w = c->body_off[k];
+      c->body_off[k] = (w >> kStEpochShift) == c->body_epoch ? (w & kStValue) : c->body_off[k + 1];
+    }
   }
   c->body_off_valid = true;
   return KGX_OK;
@@ -685,8 +823,9 @@ int kgx_create(int device, const kgx_opts* opts, kgx_ctx** out) {
   build_family_meta(c);
   if (cudaHostAlloc(reinterpret_cast<void**>(&c->h_counters), C_COUNT * 8, cudaHostAllocMapped) != cudaSuccess ||
       cudaHostGetDevicePointer(reinterpret_cast<void**>(&c->h_counters_dev), c->h_counters, 0) != cudaSuccess ||
-      dev_reserve(c, c->d_counters, C_COUNT * 8) != KGX_OK) { kgx_destroy(c); return KGX_E_CUDA; }
-  cudaMemsetAsync(c->d_counters.p, 0, C_COUNT * 8, c->stream);
+      dev_reserve(c, c->d_counters, kCounterWords * 8) != KGX_OK) { kgx_destroy(c); return KGX_E_CUDA; }
+  cudaMemsetAsync(c->d_counters.p, 0, kCounterWords * 8, c->stream);
+  memset(c->h_counters, 0, C_COUNT * 8);
   *out = c;
   return KGX_OK;
 }
@@ -715,6 +854,8 @@ int kgx_set_table(kgx_ctx* c, const kgx_table* table) {
   std::lock_guard<std::mutex> g(c->mu);
   cudaSetDevice(c->device);
   if (!table) return fail(c, KGX_E_INVAL, "null table");
+  KGX_TRY(settle_ingest(c));
+  c->reset_pending = false;  // X mode: a new table clears the window anyway
   if (c->have_table && c->mode != KGX_MODE_X &&
       (table->n_nodes != c->plan.n_nodes || table->gpus_per_node != c->plan.G))
     return fail(c, KGX_E_INVAL, "R modes: n_nodes/gpus_per_node cannot change while series persist");
@@ -800,7 +941,7 @@ int kgx_ingest_device(kgx_ctx* c, const kgx_cols* cols) {
   std::lock_guard<std::mutex> g(c->mu);
   cudaSetDevice(c->device);
   if (!cols) return fail(c, KGX_E_INVAL, "null cols");
-  return ingest_device_locked(c, cols);
+  return ingest_device_locked(c, cols);  // in flight on return: settled by the next call (see kgx.h)
 }
 
 int kgx_ingest(kgx_ctx* c, const kgx_cols* cols) {
@@ -810,6 +951,7 @@ int kgx_ingest(kgx_ctx* c, const kgx_cols* cols) {
   if (!cols) return fail(c, KGX_E_INVAL, "null cols");
   if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_ingest before kgx_set_table");
   if (!cols->gpu_total) return fail(c, KGX_E_INVAL, "cols: gpu_total missing");
+  KGX_TRY(settle_ingest(c));
   kgx_cols d = *cols;
   const size_t n = size_t(cols->n);
   if (cols->node_off) {  // the grouping promise is checked here, where the offsets are still host memory
@@ -832,7 +974,8 @@ int kgx_ingest(kgx_ctx* c, const kgx_cols* cols) {
   d.used = static_cast<const uint64_t*>(dst[2]); d.node = static_cast<const uint32_t*>(dst[3]);
   d.sm_util = static_cast<const uint32_t*>(dst[4]); d.mem_util = static_cast<const uint32_t*>(dst[5]);
   d.ts_us = static_cast<const uint64_t*>(dst[6]); d.node_off = static_cast<const uint64_t*>(dst[7]);
-  return ingest_device_locked(c, &d);
+  KGX_TRY(ingest_device_locked(c, &d));
+  return settle_ingest(c);  // the caller's buffers are free and the statistics final when this returns
 }
 
 int kgx_ingest_nvml(kgx_ctx* c, const kgx_nvml_process_info* infos, const uint64_t* dev_off, const uint64_t* gpu_total) {
@@ -843,6 +986,7 @@ int kgx_ingest_nvml(kgx_ctx* c, const kgx_nvml_process_info* infos, const uint64
   if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_ingest_nvml before kgx_set_table");
   if (!dev_off || !gpu_total) return fail(c, KGX_E_INVAL, "kgx_ingest_nvml: dev_off / gpu_total missing");
   static_assert(sizeof(kgx_nvml_process_info) == 24 && sizeof(NvmlProcessInfo) == 24, "nvmlProcessInfo_t is 24 bytes");
+  KGX_TRY(settle_ingest(c));
   const uint32_t n_dev = c->plan.n_nodes * c->plan.G;
   const size_t n = size_t(dev_off[n_dev]);
   if (dev_off[0] != 0) return fail(c, KGX_E_INVAL, "kgx_ingest_nvml: dev_off[0] must be 0");
@@ -869,7 +1013,8 @@ int kgx_ingest_nvml(kgx_ctx* c, const kgx_nvml_process_info* infos, const uint64
   d.n = n;
   d.pid = ptr<uint32_t>(c->d_cols[0]); d.gpu = ptr<uint32_t>(c->d_cols[1]); d.used = ptr<uint64_t>(c->d_cols[2]);
   d.node = ptr<uint32_t>(c->d_cols[3]); d.node_off = ptr<uint64_t>(c->d_cols[7]); d.gpu_total = gpu_total;
-  return ingest_device_locked(c, &d);
+  KGX_TRY(ingest_device_locked(c, &d));
+  return settle_ingest(c);  // the caller's buffers are free and the statistics final when this returns
 }
 
 int kgx_ingest_nvml_x(kgx_ctx* c, const kgx_nvml_process_info* infos, const uint64_t* dev_off,
@@ -882,6 +1027,7 @@ int kgx_ingest_nvml_x(kgx_ctx* c, const kgx_nvml_process_info* infos, const uint
   if (!dev_off || !util_off || !gpu_total) return fail(c, KGX_E_INVAL, "kgx_ingest_nvml_x: dev_off / util_off / gpu_total missing");
   static_assert(sizeof(kgx_nvml_process_utilization_sample) == 32 && sizeof(NvmlProcessUtilizationSample) == 32,
                 "nvmlProcessUtilizationSample_t is 32 bytes");
+  KGX_TRY(settle_ingest(c));
   const uint32_t n_dev = c->plan.n_nodes * c->plan.G;
   if (dev_off[0] != 0 || util_off[0] != 0) return fail(c, KGX_E_INVAL, "kgx_ingest_nvml_x: dev_off[0] and util_off[0] must be 0");
   for (uint32_t d = 0; d < n_dev; ++d)
@@ -920,7 +1066,8 @@ int kgx_ingest_nvml_x(kgx_ctx* c, const kgx_nvml_process_info* infos, const uint
   d.pid = ptr<uint32_t>(c->d_cols[0]); d.gpu = ptr<uint32_t>(c->d_cols[1]); d.used = ptr<uint64_t>(c->d_cols[2]);
   d.node = ptr<uint32_t>(c->d_cols[3]); d.sm_util = ptr<uint32_t>(c->d_cols[4]); d.mem_util = ptr<uint32_t>(c->d_cols[5]);
   d.ts_us = ptr<uint64_t>(c->d_cols[6]); d.node_off = ptr<uint64_t>(c->d_cols[7]); d.gpu_total = gpu_total;
-  return ingest_device_locked(c, &d);
+  KGX_TRY(ingest_device_locked(c, &d));
+  return settle_ingest(c);  // the caller's buffers are free and the statistics final when this returns
 }
 
 int kgx_reset_window(kgx_ctx* c) {
@@ -929,10 +1076,10 @@ int kgx_reset_window(kgx_ctx* c) {
   cudaSetDevice(c->device);
   if (c->mode != KGX_MODE_X) return fail(c, KGX_E_STATE, "R modes never reset: GaugeVec children persist");
   if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_reset_window before kgx_set_table");
-  Timed tm(c, KGX_K_OTHER);
-  for (int k = 0; k < 6; ++k)
-    if (c->n_series) KGX_CUDA(c, cudaMemsetAsync(c->d_acc[k].p, 0, size_t(c->n_series) * 8, c->stream));
-  KGX_CUDA(c, cudaMemsetAsync(c->d_node_live.p, 0, size_t(c->plan.n_nodes) * 4, c->stream));
+  KGX_TRY(settle_ingest(c));
+  // carried out by the next node-grouped join as it goes (each CTA clears the node it owns), or by whatever call
+  // comes first and needs the state (flush_reset)
+  c->reset_pending = true;
   c->rendered = false;
   return KGX_OK;
 }
@@ -944,13 +1091,15 @@ int kgx_expire(kgx_ctx* c, uint64_t older_than_ts_us, uint64_t* n_expired) {
   if (n_expired) *n_expired = 0;
   if (c->mode != KGX_MODE_X) return fail(c, KGX_E_STATE, "R modes never expire a series: main.go has no Delete/Reset");
   if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_expire before kgx_set_table");
+  KGX_TRY(settle_ingest(c));
+  KGX_TRY(flush_reset(c));
   if (c->n_series == 0) return KGX_OK;
-  unsigned long long* ctr = ptr<unsigned long long>(c->d_counters) + C_TICKET + 2;  // two spare counter words
+  unsigned long long* ctr = ptr<unsigned long long>(c->d_counters) + kExpireWords;  // two spare counter words
   KGX_CUDA(c, cudaMemsetAsync(ctr, 0, 16, c->stream));
   {
     Timed tm(c, KGX_K_INDEX);
     const DevAcc a = acc_view(c);
-    k_mark_expired<<<cdiv(c->n_series, 256), 256, 0, c->stream>>>(ptr<uint32_t>(c->d_ser_slot), c->n_series, a.last_ts, a.count,
+    k_mark_expired<<<cdiv(c->n_series, 256), 256, 0, c->stream>>>(ptr<uint32_t>(c->d_ser_slot), c->n_series, a.xa, a.xb,
                                                                  older_than_ts_us, ptr<uint2>(c->d_bm), ctr);
     tm.launches(1);
     KGX_TRY(launch_check(c, "k_mark_expired"));
@@ -1092,6 +1241,8 @@ int kgx_read_values(kgx_ctx* c, int family, double* values, uint32_t* slots, siz
   cudaSetDevice(c->device);
   if (!c->have_table) { *n_out = 0; return KGX_OK; }  // nothing registered yet: nothing to collect
   if (family < 0 || family >= int(c->fam.size())) return fail(c, KGX_E_INVAL, "family index out of range");
+  KGX_TRY(settle_ingest(c));
+  KGX_TRY(flush_reset(c));
   const uint32_t S = c->n_series;
   *n_out = 0;
   if (!S) return KGX_OK;
@@ -1125,6 +1276,8 @@ int kgx_read_labels(kgx_ctx* c, char* blob, size_t blob_cap, uint64_t* off, size
   std::lock_guard<std::mutex> g(c->mu);
   cudaSetDevice(c->device);
   *n_out = 0; *blob_len = 0;
+  KGX_TRY(settle_ingest(c));
+  KGX_TRY(flush_reset(c));
   if (!c->have_table || !c->n_series) { if (off && off_cap) off[0] = 0; return KGX_OK; }
   const uint32_t S = c->n_series;
   // which series carry a value (the same rule as kgx_read_values; it does not depend on the family)
@@ -1244,6 +1397,8 @@ void kgx_host_free(void* p) { if (p) cudaFreeHost(p); }
 int kgx_get_stats(kgx_ctx* c, kgx_stats* out) {
   if (!c || !out) return KGX_E_INVAL;
   std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  KGX_TRY(settle_ingest(c));
   c->stats.n_series = c->n_series;
   c->stats.device_bytes = c->device_bytes;
   *out = c->stats;
@@ -1254,6 +1409,7 @@ int kgx_sync(kgx_ctx* c) {
   if (!c) return KGX_E_INVAL;
   std::lock_guard<std::mutex> g(c->mu);
   cudaSetDevice(c->device);
+  KGX_TRY(settle_ingest(c));
   KGX_CUDA(c, cudaStreamSynchronize(c->stream));
   return KGX_OK;
 }
@@ -1350,6 +1506,8 @@ extern "C" int kgx_render_noalloc(kgx_ctx* c, uint8_t* d_out, size_t cap, size_t
   std::lock_guard<std::mutex> g(c->mu);
   cudaSetDevice(c->device);
   if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_render_noalloc before kgx_set_table");
+  KGX_TRY(settle_ingest(c));  // only a kgx_ingest_device can still be in flight here (kgx.h: kgx_sync it first)
+  KGX_TRY(flush_reset(c));
   if (c->n_tiles == 0) { *len = 0; return KGX_OK; }
   if (c->n_tiles > kNoallocMaxTiles)
     return fail(c, KGX_E_LIMIT, "kgx_render_noalloc: more render tiles than KGX_NOALLOC_MAX_TILES; use kgx_render");
@@ -1376,6 +1534,7 @@ extern "C" int kgx_render_noalloc(kgx_ctx* c, uint8_t* d_out, size_t cap, size_t
   R.tile_state = scratch + C_COUNT;
   R.node_body_off = scratch + C_COUNT + kNoallocMaxTiles;
   R.out = d_out; R.smem_bytes = c->render_smem;
+  R.epoch = 0; R.check_churn = 0; R.host_len = nullptr;  // the array was cleared above: untagged words, no hand-over
   const int grid = int(std::min<uint32_t>(c->n_tiles, uint32_t(c->render_grid)));
   if (c->render_v2) launch_writer(c, grid, R, scratch);
   else k_render<<<grid, kRenderThreads, c->render_smem, c->stream>>>(R, acc_view(c), scratch);

@@ -88,8 +88,13 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
   __shared__ Tile s_desc;      // its descriptor
   __shared__ uint32_t s_l0;    // where its first label starts inside the staged range
   const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  // the join that ran just before saw series the index does not hold yet: this body would miss them.  Every CTA leaves;
+  // the host rebuilds the index, folds what was skipped and launches again (churn only).
+  unsigned long long* ticket = ticket_of(counters, R.epoch);
+  if (R.check_churn && *(volatile unsigned long long*)&counters[C_CHURN] != 0) return;
   const uint32_t sm0 = uint32_t(__cvta_generic_to_shared(smem));
   const uint32_t bar = uint32_t(__cvta_generic_to_shared(&s_bar));
+
   // one-time: metric names of every family, with slack on both sides
   for (uint32_t i = tid; i < kMaxFamilies * kNameStride; i += THREADS) {
     const uint32_t f = i / kNameStride, o = i % kNameStride;
@@ -107,7 +112,7 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
   // ticket order and costs 3.7x; fetching the descriptor before the barrier as well measured slower, 1.601 vs
   // 1.586 ms: profiles/README.md.)
   unsigned long long tk_next = 0;
-  if (tid == 0) tk_next = atomicAdd(&counters[C_TICKET], 1ull);
+  if (tid == 0) tk_next = atomicAdd(ticket, 1ull);
   auto fetch_next = [&]() {  // warp 0: the drawn ticket, its descriptor, and the bulk copy of its label text
     const uint32_t nt = __shfl_sync(0xffffffffu, uint32_t(tk_next), 0);
     if (nt < R.n_tiles && lane == 0) {
@@ -133,7 +138,10 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
   KGX_PC_DECL;
   for (;;) {
     const uint32_t t = s_next;
-    if (t >= R.n_tiles) { KGX_PC_FLUSH; return; }
+    if (t >= R.n_tiles) {
+      KGX_PC_FLUSH;
+      return;
+    }
     const Tile tile = s_desc;
     const uint32_t l0 = s_l0;
     const FamMeta& fm = R.fam[tile.family];
@@ -178,7 +186,7 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
     const bool last_live = live && uint32_t(exc >> 48) + 1 == uint32_t(all >> 48);
     // ---- global byte offset of the tile: decoupled look-back, 32 predecessors per step.
     // Every warp resolves it for itself (same loads, same answer): no barrier, no broadcast.
-    if (tid == 0 && t > 0) atomicExch(&R.tile_state[t], kStAgg | total);
+    if (tid == 0 && t > 0) atomicExch(&R.tile_state[t], kStAgg | st_tag(R.epoch) | total);
     unsigned long long base = 0;
     if (t > 0) {
       // One step of the walk covers 32 * kLookBack predecessors: kLookBack coalesced loads of 32 consecutive look-back
@@ -191,18 +199,18 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
 #pragma unroll
         for (int k = 0; k < kLookBack; ++k) {
           const long long q = p - 32 * k;
-          st[k] = q >= 0 ? (unsigned long long)*(volatile unsigned long long*)&R.tile_state[q] : (unsigned long long)kStPrefix;  // before tile 0: prefix 0
+          st[k] = q >= 0 ? (unsigned long long)*(volatile unsigned long long*)&R.tile_state[q] : (kStPrefix | st_tag(R.epoch));  // before tile 0: prefix 0
         }
         unsigned long long v = 0;
         bool found = false;
 #pragma unroll
         for (int k = 0; k < kLookBack; ++k) {
           const long long q = p - 32 * k;
-          while ((st[k] & kStMask) == 0) st[k] = *(volatile unsigned long long*)&R.tile_state[q];  // not published yet
+          while (!st_published(st[k], R.epoch)) st[k] = *(volatile unsigned long long*)&R.tile_state[q];  // not published yet (or an older launch's word)
           const uint32_t pfx = __ballot_sync(0xffffffffu, (st[k] & kStMask) == kStPrefix);
           if (!found) {  // warp-uniform
             const uint32_t first = pfx ? uint32_t(__ffs(pfx) - 1) : 32u;
-            if (lane <= first) v += st[k] & ~kStMask;
+            if (lane <= first) v += st[k] & kStValue;
             found = pfx != 0;
           }
         }
@@ -214,9 +222,9 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
     }
     KGX_PC(3);  // look-back
     if (tid == 0) {
-      atomicExch(&R.tile_state[t], kStPrefix | (base + total));
-      if (tile.flags & 2) R.node_body_off[tile.node] = base;
-      if (t == R.n_tiles - 1) counters[C_TOTAL_LEN] = base + total;
+      atomicExch(&R.tile_state[t], kStPrefix | st_tag(R.epoch) | (base + total));
+      if (tile.flags & 2) R.node_body_off[tile.node] = st_tag(R.epoch) | base;
+      if (t == R.n_tiles - 1) { counters[C_TOTAL_LEN] = base + total; if (R.host_len) *R.host_len = base + total; }
     }
     uint8_t* gtile = R.out + base;            // first byte of the tile in the output
     uint8_t* galn = R.out + (base & ~15ull);  // 16-aligned origin: position v lives at galn + v
@@ -276,7 +284,7 @@ __global__ void __launch_bounds__(THREADS) k_render3(DevRender R, RenderLayout l
       }
     }
     KGX_PC(5);  // stream my line
-    if (tid == 0) tk_next = atomicAdd(&counters[C_TICKET], 1ull);  // in flight while the rest of the CTA finishes its lines
+    if (tid == 0) tk_next = atomicAdd(ticket, 1ull);  // in flight while the rest of the CTA finishes its lines
     __syncthreads();             // (2) label stage and value slots are free
     KGX_PC(6);  // end-of-tile barrier
     if (wid == 0) fetch_next();  // next ticket, descriptor, label copy

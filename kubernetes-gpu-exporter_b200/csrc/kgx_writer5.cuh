@@ -1,0 +1,269 @@
+// kgx_writer5.cuh — the exposition writer, software-pipelined over tiles (sm_100a).
+//
+// Same output and the same building blocks as k_render3 (kgx_writer.cuh: TMA-staged label text, one line per thread,
+// 16-byte chunks aligned to the global address, decoupled look-back over tiles handed out in output order) — what
+// changes is WHEN a tile's size is published.  In k_render3 a tile formats its values, publishes its size and at once
+// needs the sizes of its 32 predecessors, which other CTAs are formatting at that very moment: it waits for the slowest
+// of them, 41-45 % of a tile's time (profiles/README.md, round 2: phase clocks).  Here a CTA keeps two tiles in flight:
+//
+//   iteration i:   MEASURE tile t(i+1)   state loads, value text into the other slot buffer, CTA scan,
+//                                        size published                     <- a whole tile period early
+//                  EMIT    tile t(i)     look-back (the predecessors' sizes have been out for a period), header,
+//                                        stream the lines
+//                  hand-over             labels of t(i+1) -> stage (TMA), ticket + descriptor of t(i+2)
+//
+// Tickets are still drawn in output order and sizes are still published in ticket order, so the look-back never waits
+// on a tile that has not started; it just no longer waits on one that is still formatting.
+#pragma once
+#include "kgx_writer.cuh"
+
+namespace kgx {
+
+#ifndef KGX_LOOKBACK5
+#define KGX_LOOKBACK5 1
+#endif
+constexpr int kLookBack5 = KGX_LOOKBACK5;  // look-back words per lane and step (32 * kLookBack5 predecessors per step)
+
+struct LineState {  // what MEASURE leaves for EMIT, per thread
+  uint32_t len, lbl_len, vlen;  // bytes of my line, of its label text, of its value text
+  uint32_t off;                 // my line's offset inside the tile (header included)
+  uint32_t lbl_at;              // my label's offset inside the tile's label range
+  uint32_t total, hdr;          // tile bytes, header bytes (CTA-uniform)
+  bool live, first_live, last_live;
+};
+
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS) k_render5(DevRender R, RenderLayout lay, DevAcc acc, unsigned long long* counters) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ unsigned long long s_scan[THREADS / 32];
+  __shared__ uint4 s_tail;
+  __shared__ __align__(8) unsigned long long s_bar;
+  __shared__ uint32_t s_tk[2];   // tickets of the two tiles in flight
+  __shared__ Tile s_desc[2];     // their descriptors
+  __shared__ uint32_t s_l0;      // where the first label starts inside the staged range (tile being emitted)
+  const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  unsigned long long* ticket = ticket_of(counters, R.epoch);
+  if (R.check_churn && *(volatile unsigned long long*)&counters[C_CHURN] != 0) return;
+  const uint32_t sm0 = uint32_t(__cvta_generic_to_shared(smem));
+  const uint32_t bar = uint32_t(__cvta_generic_to_shared(&s_bar));
+
+  for (uint32_t i = tid; i < kMaxFamilies * kNameStride; i += THREADS) {
+    const uint32_t f = i / kNameStride, o = i % kNameStride;
+    smem[lay.names + i] = (o >= 16 && o < 16 + 64 && f < R.n_families) ? R.fam[f].name[o - 16] : uint8_t('#');
+  }
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  unsigned long long tk_next = 0;
+  // warp 0: the ticket thread 0 drew goes into pipeline slot k, with its descriptor
+  auto fetch_desc = [&](uint32_t k) {
+    const uint32_t nt = __shfl_sync(0xffffffffu, uint32_t(tk_next), 0);
+    if (lane == 0) {
+      if (nt < R.n_tiles) s_desc[k] = R.tiles[nt];
+      s_tk[k] = nt;
+    }
+  };
+  // warp 0: bulk copy of the label text of the tile in slot k into the (single) stage
+  auto issue_labels = [&](uint32_t k) {
+    if (lane == 0) {
+      const unsigned long long L0 = s_desc[k].lbl0, L1 = s_desc[k].lbl1;
+      const unsigned long long g0 = L0 & ~127ull;  // whole 128-byte lines
+      const uint32_t bytes = uint32_t(((L1 + 15ull) & ~15ull) - g0);
+      if (bytes) {
+        mbar_expect_tx(bar, bytes);
+        bulk_g2s(sm0 + lay.stage + 32, R.lbl_blob + g0, bytes, bar);
+      } else {
+        mbar_arrive(bar);
+      }
+      s_l0 = uint32_t(L0 - g0);
+    }
+  };
+
+  // ---- MEASURE the tile in pipeline slot k: value text into slot buffer k, exact line lengths, CTA scan, and the
+  // tile's size published for the look-back of its successors.  Contains one CTA barrier.
+  auto measure = [&](uint32_t k, LineState& L) {
+    const Tile tile = s_desc[k];
+    const uint32_t t = s_tk[k];
+    const FamMeta& fm = R.fam[tile.family];
+    L.len = 0; L.lbl_len = 0; L.vlen = 0; L.live = false;
+    if (tid < tile.count) {
+      const uint32_t r = tile.first + tid;
+      L.lbl_len = R.ser_len[r];
+      bool live;
+      const double v = series_value(fm.kind, acc, R, r, live);
+      L.live = live;
+      if (live) {
+        uint8_t* sp = smem + lay.slots + (k * THREADS + tid) * kSlotBytes;
+        sp[0] = ' ';
+        L.vlen = uint32_t(format_value(v, sp + 1));
+        sp[1 + L.vlen] = '\n';
+        L.len = fm.name_len + L.lbl_len + L.vlen + 2;
+      }
+    }
+    L.hdr = ((tile.flags & 1) && acc.node_live[tile.node] != 0) ? fm.header_len : 0;
+    // exclusive scan over the CTA, three fields at once: output bytes (24 bits), label bytes of every series,
+    // printed or not (24 bits), lines printed (16 bits)
+    const unsigned long long mine = (uint64_t(L.live) << 48) | (uint64_t(L.lbl_len) << 24) | L.len;
+    unsigned long long inc = mine;
+    for (int o = 1; o < 32; o <<= 1) { unsigned long long u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
+    if (lane == 31) s_scan[wid] = inc;
+    __syncthreads();
+    unsigned long long woff = 0, all = 0;
+    for (int w = 0; w < THREADS / 32; ++w) { if (w < int(wid)) woff += s_scan[w]; all += s_scan[w]; }
+    const unsigned long long exc = woff + inc - mine;
+    L.off = L.hdr + (uint32_t(exc) & 0xffffffu);
+    L.total = L.hdr + (uint32_t(all) & 0xffffffu);
+    L.lbl_at = uint32_t(exc >> 24) & 0xffffffu;
+    L.first_live = L.live && uint32_t(exc >> 48) == 0;
+    L.last_live = L.live && uint32_t(exc >> 48) + 1 == uint32_t(all >> 48);
+    if (tid == 0 && t > 0) atomicExch(&R.tile_state[t], kStAgg | st_tag(R.epoch) | L.total);
+  };
+
+  uint32_t parity = 0;
+  KGX_PC_DECL;
+  // ---- EMIT the tile in pipeline slot k (measured one iteration ago): global offset by look-back, header, lines
+  auto emit = [&](uint32_t k, const LineState& L) {
+    const Tile tile = s_desc[k];
+    const uint32_t t = s_tk[k];
+    const FamMeta& fm = R.fam[tile.family];
+    const uint32_t name_len = fm.name_len;
+    const uint32_t slot = sm0 + lay.slots + (k * THREADS + tid) * kSlotBytes;
+    // decoupled look-back, 32 predecessors per step; every warp resolves it for itself (no barrier, no broadcast)
+    unsigned long long base = 0;
+    if (t > 0) {
+      // One step covers 32 * kLookBack5 predecessors: kLookBack5 coalesced loads of 32 consecutive look-back words each
+      // (lane 0 of load 0 is the direct predecessor), all in flight together.  The predecessors' sizes were published a
+      // tile period ago, so nothing here spins; what costs is the WALK back to the nearest tile that already knows its
+      // prefix — hundreds of tickets with thousands of tiles in flight, ~18 dependent L2 round trips at 32 per step.
+      long long p = (long long)t - 1 - lane;
+      for (;;) {
+        unsigned long long st[kLookBack5];
+#pragma unroll
+        for (int q = 0; q < kLookBack5; ++q) {
+          const long long at = p - 32 * q;
+          st[q] = at >= 0 ? (unsigned long long)*(volatile unsigned long long*)&R.tile_state[at] : (kStPrefix | st_tag(R.epoch));  // before tile 0: prefix 0
+        }
+        unsigned long long v = 0;
+        bool found = false;
+#pragma unroll
+        for (int q = 0; q < kLookBack5; ++q) {
+          const long long at = p - 32 * q;
+          while (!st_published(st[q], R.epoch)) st[q] = *(volatile unsigned long long*)&R.tile_state[at];
+          const uint32_t pfx = __ballot_sync(0xffffffffu, (st[q] & kStMask) == kStPrefix);
+          if (!found) {  // warp-uniform
+            const uint32_t first = pfx ? uint32_t(__ffs(pfx) - 1) : 32u;
+            if (lane <= first) v += st[q] & kStValue;
+            found = pfx != 0;
+          }
+        }
+        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        base += v;
+        if (found) break;
+        p -= 32 * kLookBack5;
+      }
+    }
+    if (tid == 0) {
+      atomicExch(&R.tile_state[t], kStPrefix | st_tag(R.epoch) | (base + L.total));
+      if (tile.flags & 2) R.node_body_off[tile.node] = st_tag(R.epoch) | base;
+      if (t == R.n_tiles - 1) { counters[C_TOTAL_LEN] = base + L.total; if (R.host_len) *R.host_len = base + L.total; }
+    }
+    uint8_t* gtile = R.out + base;            // first byte of the tile in the output
+    uint8_t* galn = R.out + (base & ~15ull);  // 16-aligned origin: position v lives at galn + v
+    const uint32_t sh = uint32_t(base & 15);
+    if (L.hdr) for (uint32_t i = tid; i < L.hdr; i += THREADS) gtile[i] = fm.header[i];
+    KGX_PC(3);  // look-back
+    mbar_wait(bar, parity);  // the tile's label text has landed (issued during the previous iteration's hand-over)
+    parity ^= 1;
+    KGX_PC(4);  // header + label wait
+    if (L.live) {
+      const uint32_t lbl_src = sm0 + lay.stage + 32 + s_l0 + L.lbl_at;
+      const uint32_t g = sh + L.off;                                                  // first byte of my line (position)
+      const uint32_t b0 = g + name_len, b1 = b0 + L.lbl_len, b2 = b1 + L.vlen + 2;    // source boundaries; b2 = line end
+      const uint32_t start = (g + 15u) & ~15u;
+      const uint32_t stop = L.last_live ? (b2 & ~15u) : ((b2 + 15u) & ~15u);          // my full chunks: [start, stop)
+      const uint32_t name_sm = sm0 + lay.names + tile.family * kNameStride + 16;
+      const uint32_t d0 = name_sm - g, d1 = lbl_src - b0, d2 = slot - b1, d3 = name_sm - b2;  // source = position + delta
+      if (L.first_live) {  // the bytes before my first aligned chunk: nobody else writes them
+        for (uint32_t q = g; q < start && q < b2; ++q) galn[q] = smem[lay.names + tile.family * kNameStride + 16 + (q - g)];
+      }
+      uint32_t p = start, e = 0;  // `a4` holds the chunk at p, of which the first `e` bytes are already final
+      uint4 a4 = make_uint4(0, 0, 0, 0);
+      auto append = [&](uint32_t d, uint32_t b) {  // source = position + d, up to position b (exclusive)
+        uint32_t wa = (p + d) & ~3u;
+        const uint32_t r = ((p + d) & 3u) * 8u;
+        uint32_t w0 = lds32(wa), w1 = lds32(wa + 4), w2 = lds32(wa + 8), w3 = lds32(wa + 12), w4 = lds32(wa + 16);
+        auto chunk = [&]() {
+          return make_uint4(__funnelshift_r(w0, w1, r), __funnelshift_r(w1, w2, r), __funnelshift_r(w2, w3, r),
+                            __funnelshift_r(w3, w4, r));
+        };
+        auto step = [&]() { wa += 16; w0 = w4; w1 = lds32(wa + 4); w2 = lds32(wa + 8); w3 = lds32(wa + 12); w4 = lds32(wa + 16); };
+        const uint4 nw = chunk();
+        a4 = e ? merge16(a4, nw, e) : nw;
+        if (b >= p + 16) {
+          stg128_cs(galn + p, a4);
+          p += 16;
+          step();
+          while (p + 16 <= b) {
+            stg128_cs(galn + p, chunk());
+            p += 16;
+            step();
+          }
+          a4 = chunk();
+        }
+        e = b - p;
+      };
+      append(d0, b0);  // metric name
+      append(d1, b1);  // labels
+      append(d2, b2);  // " <value>\n"
+      if (!L.last_live) {
+        append(d3, stop);  // the head of the next line's name completes my last chunk
+      } else if (e) {      // the tile ends inside a chunk: its bytes belong to me, the rest to the next tile
+        s_tail = a4;
+        const uint8_t* sp = reinterpret_cast<const uint8_t*>(&s_tail);
+        for (uint32_t q = 0; q < e; ++q) galn[p + q] = sp[q];
+      }
+    }
+  };
+
+  auto leave = [&]() {
+  };
+
+  // ---- prologue: first tile measured, second ticket drawn
+  if (tid == 0) tk_next = atomicAdd(ticket, 1ull);
+  if (wid == 0) { fetch_desc(0); __syncwarp(); if (s_tk[0] < R.n_tiles) issue_labels(0); }
+  __syncthreads();
+  if (s_tk[0] >= R.n_tiles) { leave(); return; }
+  LineState cur, nxt;
+  measure(0, cur);
+  if (tid == 0) tk_next = atomicAdd(ticket, 1ull);
+  if (wid == 0) fetch_desc(1);
+  __syncthreads();
+
+  uint32_t b = 0;
+  for (;;) {
+    const bool more = s_tk[b ^ 1] < R.n_tiles;  // CTA-uniform
+    if (more) measure(b ^ 1, nxt);
+    KGX_PC(1);  // measure the next tile (state loads + format + scan)
+    emit(b, cur);
+    KGX_PC(5);  // stream my line
+    // the ticket counter's reply takes ~0.5 us under load: drawn as soon as thread 0's own line is out
+    if (tid == 0 && more) tk_next = atomicAdd(ticket, 1ull);
+    __syncthreads();  // label stage and slot buffer b are free
+    KGX_PC(6);  // end-of-tile barrier
+    if (!more) { KGX_PC_FLUSH; leave(); return; }
+    if (wid == 0) { issue_labels(b ^ 1); fetch_desc(b); }  // labels of the measured tile; ticket + descriptor of the one after
+    KGX_PC(7);  // ticket + descriptor
+    __syncthreads();  // s_tk / s_desc / s_l0 visible
+    KGX_PC(8);
+#ifdef KGX_PHASE_CLOCKS
+    ++pc_tiles;
+#endif
+    cur = nxt;
+    b ^= 1;
+  }
+}
+
+}  // namespace kgx

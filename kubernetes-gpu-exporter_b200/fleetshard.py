@@ -67,6 +67,34 @@ def max_over_ranks(value, device=None, group=None):
     return float(t.item())
 
 
+def body_checksum(t, chunk=1 << 26):
+    """64-bit position-weighted checksum of a 1-D uint8 tensor (any device): sum of byte[i] * (1 + i mod 65521) in
+    wrapping int64 arithmetic, computed where the bytes live.  Two equal checksums over a few GB of text mean the
+    bytes arrived in place; a shifted, truncated or reordered body changes it."""
+    total = 0
+    n = t.numel()
+    for lo in range(0, n, chunk):
+        hi = min(n, lo + chunk)
+        w = (torch.arange(lo, hi, device=t.device, dtype=torch.int64) % 65521) + 1
+        total = (total + int((t[lo:hi].to(torch.int64) * w).sum().item())) & 0xFFFFFFFFFFFFFFFF
+    return total
+
+
+def gather_checksums(local, group=None):
+    """Every rank's body checksum, on every rank (one small all-gather next to the lengths)."""
+    world = dist.get_world_size(group)
+    c = body_checksum(local)
+    mine = torch.tensor([c - (1 << 64) if c >= (1 << 63) else c], dtype=torch.int64, device=local.device)
+    got = [torch.zeros(1, dtype=torch.int64, device=local.device) for _ in range(world)]
+    dist.all_gather(got, mine, group=group)
+    return [int(x.item()) & 0xFFFFFFFFFFFFFFFF for x in got]
+
+
+def verify_gather(out, offsets, checksums):
+    """On the destination rank: each rank's slice of the concatenation carries that rank's own checksum."""
+    return all(body_checksum(out[int(offsets[r]):int(offsets[r + 1])]) == checksums[r] for r in range(len(checksums)))
+
+
 class DeviceBytes:
     """Zero-copy view of a raw device pointer (e.g. kgx_body_device) for torch.as_tensor."""
 

@@ -106,13 +106,22 @@ class Exporter {
   // prometheus.Collector
   void Describe(std::vector<const Desc*>& ch) const { for (const Desc& d : descs_) ch.push_back(&d); }
   void Collect(std::vector<Metric>& ch) {
+    // label text of every series in one call (two device->host copies), parsed once and shared by all families:
+    // entry i of kgx_read_labels belongs to value i of every family
+    size_t n_lbl = 0, blob_len = 0;
+    check(kgx_read_labels(ctx_, nullptr, 0, nullptr, 0, &n_lbl, &blob_len));
+    std::string blob(blob_len, '\0');
+    std::vector<uint64_t> off(n_lbl + 1);
+    check(kgx_read_labels(ctx_, blob.empty() ? nullptr : &blob[0], blob.size(), off.data(), off.size(), &n_lbl, &blob_len));
+    std::vector<std::vector<std::string>> labels(n_lbl);
+    for (size_t i = 0; i < n_lbl; ++i) labels[i] = label_values(blob.data() + off[i], size_t(off[i + 1] - off[i]));
     for (size_t f = 0; f < descs_.size(); ++f) {
       size_t n = 0;
       kgx_read_values(ctx_, int(f), nullptr, nullptr, 0, &n);
       std::vector<double> v(n);
-      std::vector<uint32_t> slot(n);
-      if (n) check(kgx_read_values(ctx_, int(f), v.data(), slot.data(), n, &n));
-      for (size_t i = 0; i < n; ++i) ch.push_back(Metric{&descs_[f], v[i], label_values(slot[i])});
+      if (n) check(kgx_read_values(ctx_, int(f), v.data(), nullptr, n, &n));
+      if (n != n_lbl) throw std::runtime_error("Collect: values and labels disagree");
+      for (size_t i = 0; i < n; ++i) ch.push_back(Metric{&descs_[f], v[i], labels[i]});
     }
   }
 
@@ -131,12 +140,8 @@ class Exporter {
   void check(int rc) { if (rc != KGX_OK) throw std::runtime_error(std::string(kgx_strerror(rc)) + ": " + kgx_last_error(ctx_)); }
 
   // `{a="x",b="y"}` (escaped as expfmt writes it) back to raw label values
-  std::vector<std::string> label_values(uint32_t slot) {
-    std::string s(256, '\0');
-    size_t len = 0;
-    kgx_slot_labels(ctx_, slot, &s[0], s.size(), &len);
-    if (len > s.size()) { s.resize(len); kgx_slot_labels(ctx_, slot, &s[0], s.size(), &len); }
-    s.resize(len);
+  static std::vector<std::string> label_values(const char* p, size_t len) {
+    const std::string s(p, len);
     std::vector<std::string> out;
     size_t i = 0;
     while ((i = s.find("=\"", i)) != std::string::npos) {

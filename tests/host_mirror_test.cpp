@@ -1,6 +1,7 @@
 // Drives the C++ host mirror (kubernetes-gpu-exporter_b200/host/exporter.hpp)
 // the way main.go drives its GaugeVecs and handler, and checks the served body
 // against the hand-derived golden of SURVEY.md section 8c.  Needs a GPU.
+#include <chrono>
 #include <cstdio>
 #include <fstream>
 #include <iostream>
@@ -12,8 +13,65 @@ using namespace kgx_host;
 
 #define CHECK(c) do { if (!(c)) { std::fprintf(stderr, "CHECK failed: %s (line %d)\n", #c, __LINE__); return 1; } } while (0)
 
+// Collect over a million series (the size of BASELINE config 3): values and label text come back through the bulk
+// read-back calls, not one call per series.  Prints the time of the library calls and of the whole Collect.
+static int big_collect() {
+  const uint64_t GiB = 1ull << 30;
+  const uint32_t n_pods = 131072, per_pod = 8, n_dev = 8;
+  PodPIDMap m;
+  std::vector<Device> devs(n_dev);
+  uint32_t pid = 300;
+  for (uint32_t p = 0; p < n_pods; ++p) {
+    std::vector<std::string>& v = m["pod-" + std::to_string(p)];
+    for (uint32_t k = 0; k < per_pod; ++k, ++pid) {
+      v.push_back(std::to_string(pid));
+      devs[pid % n_dev].processInfos.push_back(ProcessInfo{pid, (uint64_t(pid) % 4096 + 1) * (2ull << 20)});
+    }
+  }
+  for (Device& d : devs) d.memoryInfo.Total = 192 * GiB;
+  Exporter ex(0, false);
+  ex.Cycle(m, devs);
+  std::vector<Metric> ms;
+  ex.Collect(ms);  // warm-up (buffers)
+  ms.clear();
+  const auto t0 = std::chrono::steady_clock::now();
+  size_t n = 0, nb = 0;
+  kgx_read_labels(ex.ctx(), nullptr, 0, nullptr, 0, &n, &nb);
+  std::string blob(nb, '\0');
+  std::vector<uint64_t> off(n + 1);
+  CHECK(kgx_read_labels(ex.ctx(), &blob[0], blob.size(), off.data(), off.size(), &n, &nb) == KGX_OK);
+  std::vector<double> v0(n), v1(n);
+  size_t n0 = 0, n1 = 0;
+  CHECK(kgx_read_values(ex.ctx(), 0, v0.data(), nullptr, n, &n0) == KGX_OK && kgx_read_values(ex.ctx(), 1, v1.data(), nullptr, n, &n1) == KGX_OK);
+  const auto t1 = std::chrono::steady_clock::now();
+  ex.Collect(ms);
+  const auto t2 = std::chrono::steady_clock::now();
+  const double lib_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+  const double all_ms = std::chrono::duration<double, std::milli>(t2 - t1).count();
+  std::printf("collect of %zu series: read-back through the C ABI %.1f ms, whole Collect (with label parsing) %.1f ms\n", n, lib_ms, all_ms);
+  CHECK(n == size_t(n_pods) * per_pod && n0 == n && n1 == n && ms.size() == 2 * n);
+  CHECK(lib_ms < 100.0);
+  // series order is by (pid as a string, pod): the first one is pid "1000000"'s neighbourhood; check a few by lookup
+  size_t seen = 0;
+  for (size_t i = 0; i < n; i += 50021) {
+    const Metric& a = ms[i];          // family 0 (percentage)
+    const Metric& b = ms[n + i];      // family 1 (bytes), same series
+    CHECK(a.labelValues == b.labelValues && a.labelValues.size() == 2);
+    const uint32_t p = uint32_t(std::stoul(a.labelValues[0]));
+    const uint64_t used = (uint64_t(p) % 4096 + 1) * (2ull << 20);
+    CHECK(a.labelValues[1] == "pod-" + std::to_string((p - 300) / per_pod));
+    CHECK(b.value == double(used) && a.value == double(used) / double(192 * GiB) * 100);
+    CHECK(b.value == v1[i] && a.value == v0[i]);
+    ++seen;
+  }
+  CHECK(seen > 10);
+  std::puts("ok");
+  return 0;
+}
+
 int main(int argc, char** argv) {
   if (argc < 2) return 2;
+  if (std::string(argv[1]) == "big") return big_collect();
   std::ifstream f(argv[1], std::ios::binary);
   std::stringstream golden;
   golden << f.rdbuf();

@@ -29,3 +29,13 @@ def test_host_mirror_serves_the_golden_body(tmp_path):
     exe = _compile(tmp_path)
     r = subprocess.run([exe, os.path.join(ROOT, "tests", "golden", "r_single.txt")], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and r.stdout.strip() == "ok", r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_host_mirror_collects_a_million_series_in_bulk(tmp_path):
+    """prometheus.Collector.Collect over 1 M series (BASELINE config 3's size): the read-back through the C ABI (labels
+    in one call, values one call per family) stays under 100 ms; values and label values are checked by recomputation."""
+    exe = _compile(tmp_path)
+    r = subprocess.run([exe, "big"], capture_output=True, text=True, timeout=300)
+    print(r.stdout)
+    assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout + r.stderr

@@ -119,8 +119,9 @@ def test_noalloc_rejects_sizes_beyond_its_scratch():
     assert rc == abi.KGX_E_LIMIT
     assert b"KGX_NOALLOC_MAX_NODES" in kgx.lib().kgx_last_error(g._h)
     assert g.render().startswith(b"# HELP")           # the allocating entry point still serves it
-    # within the node limit but more render tiles than KGX_NOALLOC_MAX_TILES (65 536): 4 000 nodes x 2 families x 10
-    f = Fleet(n_nodes=4000, pods=100, procs=600, seed=0xB200 + 34)
+    # within the node limit but more render tiles than KGX_NOALLOC_MAX_TILES (65 536): 4 000 nodes x 2 families x 11
+    # tiles of up to 128 series
+    f = Fleet(n_nodes=4000, pods=100, procs=1400, seed=0xB200 + 34)
     g = kgx.Kgx(MODE_R_INTENDED)
     g.set_table(f.table(MODE_R_INTENDED))
     g.ingest(f.scrape(0))

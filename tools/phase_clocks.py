@@ -24,7 +24,7 @@ if __name__ == "__main__":
         build.build_variant(SO, ["-DKGX_PHASE_CLOCKS"])
         print("built", SO)
         sys.exit(0)
-    os.environ["KGX_LIB"] = SO
+    os.environ.setdefault("KGX_LIB", SO)
     import kgx_loader
     kgx_loader.load()
     import numpy as np
