@@ -18,9 +18,14 @@
  *     main.go:47,59,79,119);
  *   - the caller owns every buffer it passes in; the library copies what it
  *     needs before returning and owns all device memory;
- *   - one kgx_ctx per GPU, no global state; calls on one ctx are serialised
- *     by the library (one writer, any number of readers; readers see the
- *     last completed ingest).
+ *   - one kgx_ctx per GPU, no global state; calls on one ctx may come from
+ *     any number of threads (the reference polls in one goroutine and serves
+ *     scrapes in others, main.go:68-74).  Calls that touch the series state
+ *     are serialised by the library: one writer, any number of readers, and
+ *     a reader sees the last COMPLETED ingest.  kgx_ingest copies its batch
+ *     to the GPU before it takes that lock, so a scrape never waits for a
+ *     batch in transit, only for a join that is actually running;
+ *   - kgx_last_error is per calling thread;
  *   - there is NO CPU fallback: without a CUDA device kgx_create fails with
  *     KGX_E_CUDA.
  */
@@ -369,7 +374,7 @@ int kgx_set_profile(kgx_ctx* ctx, int on);
 int kgx_sync(kgx_ctx* ctx);
 
 const char* kgx_strerror(int code);
-/* Detail of the last error on ctx (valid until the next call on ctx). */
+/* Detail of the last error of the CALLING THREAD (valid until its next call into the library). */
 const char* kgx_last_error(kgx_ctx* ctx);
 int kgx_abi_version(void);
 

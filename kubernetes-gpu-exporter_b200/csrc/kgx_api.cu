@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cstdio>
 #include <cstring>
@@ -42,10 +43,15 @@ struct kgx_ctx {
   // is rendered into the other (kgx_render_begin).  *_busy: a copy started by kgx_render_begin still reads that buffer.
   cudaEvent_t ev_copy_out = nullptr, ev_copy_alt = nullptr;
   bool out_busy = false, alt_busy = false;
-  std::mutex mu;
-  std::string err;
+  // mu serialises everything that touches the series state (one writer, any number of readers: a reader sees the last
+  // completed ingest).  mu_in only guards the staging of a kgx_ingest batch (host->device copies into d_cols on
+  // in_stream): that part runs WITHOUT mu, so a scrape never waits for a batch that is still being copied in, only
+  // for a join that is actually running.  Lock order: mu_in, then mu.
+  std::mutex mu, mu_in;
+  cudaStream_t in_stream = nullptr;
+  uint64_t table_gen = 0;  // bumped by kgx_set_table
   int sm_count = 148;
-  size_t device_bytes = 0;
+  std::atomic<size_t> device_bytes{0};
 
   bool have_table = false;
   Plan plan;
@@ -79,9 +85,8 @@ struct kgx_ctx {
   DBuf d_fam, d_tiles, d_tile_state, d_node_body_off, d_out, d_out_alt;
   uint32_t n_tiles = 0, tile_lines = 0, render_smem = 0;
   bool render_v2 = false;  // second-generation writer (needs metric names of 15..64 bytes)
-  int writer_gen = 5;      // 5: k_render5 (two tiles in flight per CTA, the default); 3: k_render3 (one tile at a time)
   RenderLayout lay{};
-  int render_grid = 0, render_threads = 64;   // measured best on B200: direct stores, 64-line tiles
+  int render_grid = 0, render_threads = 128;  // measured best on B200: direct stores, 128-line tiles
   size_t last_len = 0;
   bool rendered = false;
   std::vector<uint64_t> body_off;  // host copy of the last body's per-node offsets (kgx_body_node), fetched on first use
@@ -91,7 +96,7 @@ struct kgx_ctx {
   DBuf d_counters;
   unsigned long long* h_counters = nullptr;  // pinned and mapped: kernels post results here (k_post_words)
   unsigned long long* h_counters_dev = nullptr;  // its device alias
-  DBuf d_cols[8];
+  DBuf d_cols[9];  // staging of a kgx_ingest batch (guarded by mu_in): the seven columns, node_off, gpu_total
   DBuf d_tmp[6];
   uint32_t seq = 0;
   // kgx_ingest_device returns once its kernels are queued: the statistics and the churn check of that join are
@@ -114,11 +119,16 @@ constexpr int kExpireWords = 8;
 const char* const kErrNames[] = {"ok", "invalid argument", "out of memory", "CUDA error", "output buffer too small",
                                  "call out of order", "size beyond a documented maximum"};
 
+// Detail of the last error, per calling thread: the poll loop and the scrape handlers call into one ctx concurrently
+// and must not see (or tear) each other's message.
+thread_local std::string tl_err;
+
 #define KGX_CUDA(c, call)                                                                      \
   do {                                                                                         \
     cudaError_t e_ = (call);                                                                   \
     if (e_ != cudaSuccess) {                                                                   \
-      (c)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                           \
+      (void)(c);                                                                               \
+      tl_err = std::string(#call) + ": " + cudaGetErrorString(e_);                             \
       return e_ == cudaErrorMemoryAllocation ? KGX_E_NOMEM : KGX_E_CUDA;                       \
     }                                                                                          \
   } while (0)
@@ -129,7 +139,7 @@ const char* const kErrNames[] = {"ok", "invalid argument", "out of memory", "CUD
     if (rc_ != KGX_OK) return rc_; \
   } while (0)
 
-int fail(kgx_ctx* c, int code, const char* msg) { c->err = msg; return code; }
+int fail(kgx_ctx*, int code, const char* msg) { tl_err = msg; return code; }
 
 int dev_reserve(kgx_ctx* c, DBuf& b, size_t bytes) {
   if (bytes <= b.cap && b.p) return KGX_OK;
@@ -174,7 +184,7 @@ void wait_copy(kgx_ctx* c) {
 
 int launch_check(kgx_ctx* c, const char* what) {
   cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) { c->err = std::string(what) + ": " + cudaGetErrorString(e); return KGX_E_CUDA; }
+  if (e != cudaSuccess) { (void)c; tl_err = std::string(what) + ": " + cudaGetErrorString(e); return KGX_E_CUDA; }
   return KGX_OK;
 }
 
@@ -209,36 +219,21 @@ DevAcc acc_view(kgx_ctx* c) {
 int n_acc_arrays(const kgx_ctx* c) { return c->mode == KGX_MODE_X ? 2 : 3; }  // X: xa, xb (kgx_kernels.cuh)
 int acc_words(const kgx_ctx* c, int k) { return c->mode == KGX_MODE_X ? (k == 0 ? int(kXAWords) : int(kXBWords)) : 1; }  // words per series
 
-// the writer is compiled for four CTA sizes (= lines per tile); 64 measured best on B200
+// the writer is compiled for four CTA sizes (= lines per tile); 128 measured best on B200
 const void* writer_func(const kgx_ctx* c) {
-  if (c->writer_gen == 5) switch (c->render_threads) {
-    case 32: return reinterpret_cast<const void*>(&k_render5<32>);
-    case 128: return reinterpret_cast<const void*>(&k_render5<128>);
-    case 256: return reinterpret_cast<const void*>(&k_render5<256>);
-    default: return reinterpret_cast<const void*>(&k_render5<64>);
-  }
   switch (c->render_threads) {
-    case 32: return reinterpret_cast<const void*>(&k_render3<32>);
-    case 128: return reinterpret_cast<const void*>(&k_render3<128>);
-    case 256: return reinterpret_cast<const void*>(&k_render3<256>);
-    default: return reinterpret_cast<const void*>(&k_render3<64>);
+    case 32: return reinterpret_cast<const void*>(&k_render5<32>);
+    case 64: return reinterpret_cast<const void*>(&k_render5<64>);
+    case 256: return reinterpret_cast<const void*>(&k_render5<256>);
+    default: return reinterpret_cast<const void*>(&k_render5<128>);
   }
 }
 void launch_writer(kgx_ctx* c, int grid, const DevRender& R, unsigned long long* counters) {
-  if (c->writer_gen == 5) {
-    switch (c->render_threads) {
-      case 32: k_render5<32><<<grid, 32, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
-      case 128: k_render5<128><<<grid, 128, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
-      case 256: k_render5<256><<<grid, 256, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
-      default: k_render5<64><<<grid, 64, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
-    }
-    return;
-  }
   switch (c->render_threads) {
-    case 32: k_render3<32><<<grid, 32, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
-    case 128: k_render3<128><<<grid, 128, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
-    case 256: k_render3<256><<<grid, 256, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
-    default: k_render3<64><<<grid, 64, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+    case 32: k_render5<32><<<grid, 32, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+    case 64: k_render5<64><<<grid, 64, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+    case 256: k_render5<256><<<grid, 256, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
+    default: k_render5<128><<<grid, 128, c->render_smem, c->stream>>>(R, c->lay, acc_view(c), counters); break;
   }
 }
 
@@ -504,13 +499,11 @@ int finish_plan(kgx_ctx* c) {
   int occ = 1;
   if (c->render_v2) {
     // per line: value slot + staged label.  Small CTAs: many independent tiles per SM hide each other's latencies
-    if (const char* e = getenv("KGX_WRITER")) c->writer_gen = atoi(e) == 3 ? 3 : 5;
-    // lines per tile = threads per CTA; measured best on B200: 128 for the pipelined writer, 64 for k_render3
-    c->render_threads = c->writer_gen == 5 ? 128 : 64;
+    // lines per tile = threads per CTA; measured best on B200: 128
+    c->render_threads = 128;
     if (const char* e = getenv("KGX_RENDER_THREADS")) c->render_threads = atoi(e);
-    if (c->render_threads != 32 && c->render_threads != 64 && c->render_threads != 128 && c->render_threads != 256)
-      c->render_threads = c->writer_gen == 5 ? 128 : 64;
-    const uint64_t slot_bufs = c->writer_gen == 5 ? 2 : 1;
+    if (c->render_threads != 32 && c->render_threads != 64 && c->render_threads != 256) c->render_threads = 128;
+    const uint64_t slot_bufs = 2;  // the tile being emitted and the one being measured
     const uint64_t fixed = uint64_t(kMaxFamilies) * kNameStride + slot_bufs * c->render_threads * kSlotBytes + 32 + (32 + 128 + 48) + 32;
     uint64_t budget = 200 * 1024;
     if (fixed + p.max_label_len > budget) return fail(c, KGX_E_LIMIT, "label text too long for one render tile");
@@ -804,7 +797,7 @@ const char* kgx_strerror(int code) {
   return (i >= 0 && i < int(sizeof kErrNames / sizeof kErrNames[0])) ? kErrNames[i] : "unknown error";
 }
 
-const char* kgx_last_error(kgx_ctx* c) { return c ? c->err.c_str() : "null ctx"; }
+const char* kgx_last_error(kgx_ctx* c) { return c ? tl_err.c_str() : "null ctx"; }
 
 int kgx_create(int device, const kgx_opts* opts, kgx_ctx** out) {
   if (!out || !opts) return KGX_E_INVAL;
@@ -842,6 +835,7 @@ void kgx_destroy(kgx_ctx* c) {
   for (auto& r : c->regions) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
   if (c->h_counters) cudaFreeHost(c->h_counters);
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+  if (c->in_stream) cudaStreamDestroy(c->in_stream);
   if (c->ev_rendered) cudaEventDestroy(c->ev_rendered);
   if (c->ev_copy_out) cudaEventDestroy(c->ev_copy_out);
   if (c->ev_copy_alt) cudaEventDestroy(c->ev_copy_alt);
@@ -874,6 +868,7 @@ int kgx_set_table(kgx_ctx* c, const kgx_table* table) {
     c->have_table = false;  // the old table's buffers are gone; the new one counts only once its geometry is set
     KGX_TRY(finish_plan(c));
     c->have_table = true;
+    c->table_gen += 1;
     c->stats.n_slots = c->plan.n_slots;
     if (cd.n) {  // R modes: series that already had a value keep it (main.go never deletes a GaugeVec child)
       k_set_bits<<<cdiv(cd.n, 256), 256, 0, c->stream>>>(cd.slot, cd.n, ptr<uint32_t>(c->d_pending));
@@ -904,7 +899,7 @@ int kgx_set_table(kgx_ctx* c, const kgx_table* table) {
   Plan np;
   std::string err;
   int rc = build_plan(c->mode, table, carried, &np, &err);
-  if (rc != KGX_OK) { c->err = err; return rc; }
+  if (rc != KGX_OK) { tl_err = err; return rc; }
   const auto t2 = now();
   reset_table_state(c);
   c->plan = std::move(np);
@@ -912,6 +907,7 @@ int kgx_set_table(kgx_ctx* c, const kgx_table* table) {
   KGX_TRY(upload_plan(c));
   KGX_TRY(finish_plan(c));
   c->have_table = true;
+  c->table_gen += 1;
   const auto t3 = now();
   c->stats.n_slots = c->plan.n_slots;
   if (!carried.empty()) {
@@ -946,40 +942,54 @@ int kgx_ingest_device(kgx_ctx* c, const kgx_cols* cols) {
 
 int kgx_ingest(kgx_ctx* c, const kgx_cols* cols) {
   if (!c) return KGX_E_INVAL;
-  std::lock_guard<std::mutex> g(c->mu);
+  std::lock_guard<std::mutex> gin(c->mu_in);  // one batch is staged at a time
   cudaSetDevice(c->device);
   if (!cols) return fail(c, KGX_E_INVAL, "null cols");
-  if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_ingest before kgx_set_table");
+  uint32_t NN = 0, G = 0;
+  uint64_t gen = 0;
+  {
+    std::lock_guard<std::mutex> g(c->mu);
+    if (!c->have_table) return fail(c, KGX_E_STATE, "kgx_ingest before kgx_set_table");
+    KGX_TRY(settle_ingest(c));  // a kgx_ingest_device batch still in flight may be reading d_cols
+    NN = c->plan.n_nodes; G = c->plan.G; gen = c->table_gen;
+  }
   if (!cols->gpu_total) return fail(c, KGX_E_INVAL, "cols: gpu_total missing");
-  KGX_TRY(settle_ingest(c));
   kgx_cols d = *cols;
   const size_t n = size_t(cols->n);
   if (cols->node_off) {  // the grouping promise is checked here, where the offsets are still host memory
-    const uint32_t NN = c->plan.n_nodes;
     if (cols->node_off[0] != 0 || cols->node_off[NN] != n) return fail(c, KGX_E_INVAL, "cols: node_off must start at 0 and end at n");
     for (uint32_t k = 0; k < NN; ++k)
       if (cols->node_off[k + 1] < cols->node_off[k]) return fail(c, KGX_E_INVAL, "cols: node_off not ascending");
   }
-  const void* src[8] = {cols->pid, cols->gpu, cols->used, cols->node, cols->sm_util, cols->mem_util, cols->ts_us, cols->node_off};
-  const size_t bytes[8] = {n * 4, n * 4, n * 8, n * 4, n * 4, n * 4, n * 8, (size_t(c->plan.n_nodes) + 1) * 8};
-  const void* dst[8];
-  for (int k = 0; k < 8; ++k) {
+  // Stage the batch on the copy-in stream, WITHOUT the state mutex: scrapes go on rendering the last completed
+  // reduction while hundreds of megabytes cross PCIe (the reference's HTTP goroutines likewise never wait for the poll
+  // loop's I/O, main.go:68-74).
+  if (!c->in_stream) KGX_CUDA(c, cudaStreamCreateWithFlags(&c->in_stream, cudaStreamNonBlocking));
+  const void* src[9] = {cols->pid, cols->gpu, cols->used, cols->node, cols->sm_util, cols->mem_util, cols->ts_us, cols->node_off, cols->gpu_total};
+  const size_t bytes[9] = {n * 4, n * 4, n * 8, n * 4, n * 4, n * 4, n * 8, (size_t(NN) + 1) * 8, size_t(NN) * G * 8};
+  const void* dst[9];
+  for (int k = 0; k < 9; ++k) {
     dst[k] = nullptr;
     if (!src[k]) continue;
     KGX_TRY(dev_reserve(c, c->d_cols[k], bytes[k]));
-    if (bytes[k]) KGX_CUDA(c, cudaMemcpyAsync(c->d_cols[k].p, src[k], bytes[k], cudaMemcpyHostToDevice, c->stream));
+    if (bytes[k]) KGX_CUDA(c, cudaMemcpyAsync(c->d_cols[k].p, src[k], bytes[k], cudaMemcpyHostToDevice, c->in_stream));
     dst[k] = c->d_cols[k].p;
   }
+  KGX_CUDA(c, cudaStreamSynchronize(c->in_stream));  // the caller's buffers are free from here on
   d.pid = static_cast<const uint32_t*>(dst[0]); d.gpu = static_cast<const uint32_t*>(dst[1]);
   d.used = static_cast<const uint64_t*>(dst[2]); d.node = static_cast<const uint32_t*>(dst[3]);
   d.sm_util = static_cast<const uint32_t*>(dst[4]); d.mem_util = static_cast<const uint32_t*>(dst[5]);
   d.ts_us = static_cast<const uint64_t*>(dst[6]); d.node_off = static_cast<const uint64_t*>(dst[7]);
+  d.gpu_total = static_cast<const uint64_t*>(dst[8]);
+  std::lock_guard<std::mutex> g(c->mu);
+  if (c->table_gen != gen || !c->have_table) return fail(c, KGX_E_STATE, "kgx_set_table ran while this batch was being copied in");
   KGX_TRY(ingest_device_locked(c, &d));
-  return settle_ingest(c);  // the caller's buffers are free and the statistics final when this returns
+  return settle_ingest(c);  // the statistics are final when this returns
 }
 
 int kgx_ingest_nvml(kgx_ctx* c, const kgx_nvml_process_info* infos, const uint64_t* dev_off, const uint64_t* gpu_total) {
   if (!c) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> gin(c->mu_in);  // the staging buffers are shared with kgx_ingest
   std::lock_guard<std::mutex> g(c->mu);
   cudaSetDevice(c->device);
   if (c->mode == KGX_MODE_X) return fail(c, KGX_E_STATE, "kgx_ingest_nvml: nvmlProcessInfo_t carries no utilisation or timestamp; R modes only");
@@ -1020,6 +1030,7 @@ int kgx_ingest_nvml(kgx_ctx* c, const kgx_nvml_process_info* infos, const uint64
 int kgx_ingest_nvml_x(kgx_ctx* c, const kgx_nvml_process_info* infos, const uint64_t* dev_off,
                       const kgx_nvml_process_utilization_sample* utils, const uint64_t* util_off, const uint64_t* gpu_total) {
   if (!c) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> gin(c->mu_in);  // the staging buffers are shared with kgx_ingest
   std::lock_guard<std::mutex> g(c->mu);
   cudaSetDevice(c->device);
   if (c->mode != KGX_MODE_X) return fail(c, KGX_E_STATE, "kgx_ingest_nvml_x: X mode only (R modes take kgx_ingest_nvml)");

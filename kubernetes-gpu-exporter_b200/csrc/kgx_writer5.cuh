@@ -1,10 +1,11 @@
 // kgx_writer5.cuh — the exposition writer, software-pipelined over tiles (sm_100a).
 //
-// Same output and the same building blocks as k_render3 (kgx_writer.cuh: TMA-staged label text, one line per thread,
-// 16-byte chunks aligned to the global address, decoupled look-back over tiles handed out in output order) — what
-// changes is WHEN a tile's size is published.  In k_render3 a tile formats its values, publishes its size and at once
-// needs the sizes of its 32 predecessors, which other CTAs are formatting at that very moment: it waits for the slowest
-// of them, 41-45 % of a tile's time (profiles/README.md, round 2: phase clocks).  Here a CTA keeps two tiles in flight:
+// The building blocks are described in kgx_writer.cuh (TMA-staged label text, one line per thread, 16-byte chunks
+// aligned to the global address, decoupled look-back over tiles handed out in output order).  What this kernel adds is
+// WHEN a tile's size is published.  A writer that formats a tile's values, publishes its size and at once needs the
+// sizes of its 32 predecessors finds other CTAs formatting those at that very moment: it waits for the slowest of them,
+// 41-45 % of a tile's time (round 1's k_render3; profiles/README.md, round 2: phase clocks).  Here a CTA keeps two tiles
+// in flight:
 //
 //   iteration i:   MEASURE tile t(i+1)   state loads, value text into the other slot buffer, CTA scan,
 //                                        size published                     <- a whole tile period early
@@ -26,14 +27,17 @@ constexpr int kLookBack5 = KGX_LOOKBACK5;  // look-back words per lane and step 
 
 struct LineState {  // what MEASURE leaves for EMIT, per thread
   uint32_t len, lbl_len, vlen;  // bytes of my line, of its label text, of its value text
+  uint32_t vstart;              // where " <value>\n" starts inside my value slot (format_slot)
   uint32_t off;                 // my line's offset inside the tile (header included)
   uint32_t lbl_at;              // my label's offset inside the tile's label range
   uint32_t total, hdr;          // tile bytes, header bytes (CTA-uniform)
   bool live, first_live, last_live;
 };
 
+// 1 280 resident threads per SM is what shared memory allows with 128-line tiles (10 CTAs): the register budget is
+// pinned to that (48 per thread), or two more registers would cost a whole CTA per SM.
 template <int THREADS>
-__global__ void __launch_bounds__(THREADS) k_render5(DevRender R, RenderLayout lay, DevAcc acc, unsigned long long* counters) {
+__global__ void __launch_bounds__(THREADS, (1280 / THREADS < 32 ? 1280 / THREADS : 32)) k_render5(DevRender R, RenderLayout lay, DevAcc acc, unsigned long long* counters) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ unsigned long long s_scan[THREADS / 32];
   __shared__ uint4 s_tail;
@@ -88,7 +92,7 @@ __global__ void __launch_bounds__(THREADS) k_render5(DevRender R, RenderLayout l
     const Tile tile = s_desc[k];
     const uint32_t t = s_tk[k];
     const FamMeta& fm = R.fam[tile.family];
-    L.len = 0; L.lbl_len = 0; L.vlen = 0; L.live = false;
+    L.len = 0; L.lbl_len = 0; L.vlen = 0; L.vstart = 0; L.live = false;
     if (tid < tile.count) {
       const uint32_t r = tile.first + tid;
       L.lbl_len = R.ser_len[r];
@@ -96,10 +100,9 @@ __global__ void __launch_bounds__(THREADS) k_render5(DevRender R, RenderLayout l
       const double v = series_value(fm.kind, acc, R, r, live);
       L.live = live;
       if (live) {
-        uint8_t* sp = smem + lay.slots + (k * THREADS + tid) * kSlotBytes;
-        sp[0] = ' ';
-        L.vlen = uint32_t(format_value(v, sp + 1));
-        sp[1 + L.vlen] = '\n';
+        uint32_t vs;
+        L.vlen = format_slot(v, smem + lay.slots + (k * THREADS + tid) * kSlotBytes, vs);
+        L.vstart = vs - 1;  // the space before the value
         L.len = fm.name_len + L.lbl_len + L.vlen + 2;
       }
     }
@@ -185,7 +188,7 @@ __global__ void __launch_bounds__(THREADS) k_render5(DevRender R, RenderLayout l
       const uint32_t start = (g + 15u) & ~15u;
       const uint32_t stop = L.last_live ? (b2 & ~15u) : ((b2 + 15u) & ~15u);          // my full chunks: [start, stop)
       const uint32_t name_sm = sm0 + lay.names + tile.family * kNameStride + 16;
-      const uint32_t d0 = name_sm - g, d1 = lbl_src - b0, d2 = slot - b1, d3 = name_sm - b2;  // source = position + delta
+      const uint32_t d0 = name_sm - g, d1 = lbl_src - b0, d2 = slot + L.vstart - b1, d3 = name_sm - b2;  // source = position + delta
       if (L.first_live) {  // the bytes before my first aligned chunk: nobody else writes them
         for (uint32_t q = g; q < start && q < b2; ++q) galn[q] = smem[lay.names + tile.family * kNameStride + 16 + (q - g)];
       }
@@ -228,14 +231,11 @@ __global__ void __launch_bounds__(THREADS) k_render5(DevRender R, RenderLayout l
     }
   };
 
-  auto leave = [&]() {
-  };
-
   // ---- prologue: first tile measured, second ticket drawn
   if (tid == 0) tk_next = atomicAdd(ticket, 1ull);
   if (wid == 0) { fetch_desc(0); __syncwarp(); if (s_tk[0] < R.n_tiles) issue_labels(0); }
   __syncthreads();
-  if (s_tk[0] >= R.n_tiles) { leave(); return; }
+  if (s_tk[0] >= R.n_tiles) return;
   LineState cur, nxt;
   measure(0, cur);
   if (tid == 0) tk_next = atomicAdd(ticket, 1ull);
@@ -249,11 +249,13 @@ __global__ void __launch_bounds__(THREADS) k_render5(DevRender R, RenderLayout l
     KGX_PC(1);  // measure the next tile (state loads + format + scan)
     emit(b, cur);
     KGX_PC(5);  // stream my line
-    // the ticket counter's reply takes ~0.5 us under load: drawn as soon as thread 0's own line is out
+    // the ticket counter's reply takes ~0.5 us under load: drawn as soon as thread 0's own line is out.  (Drawing it a
+    // whole iteration ahead, descriptor loaded between MEASURE and EMIT, hides that latency but lets tiles drift out
+    // of ticket order: 1.42 -> 1.59 ms, profiles/README.md round 2.)
     if (tid == 0 && more) tk_next = atomicAdd(ticket, 1ull);
     __syncthreads();  // label stage and slot buffer b are free
     KGX_PC(6);  // end-of-tile barrier
-    if (!more) { KGX_PC_FLUSH; leave(); return; }
+    if (!more) { KGX_PC_FLUSH; return; }
     if (wid == 0) { issue_labels(b ^ 1); fetch_desc(b); }  // labels of the measured tile; ticket + descriptor of the one after
     KGX_PC(7);  // ticket + descriptor
     __syncthreads();  // s_tk / s_desc / s_l0 visible

@@ -300,6 +300,58 @@ def test_concurrent_scrapes_while_polling(kgo):
     assert sum(len(s) for s in seen) >= 3  # the readers did run
 
 
+def test_scrapes_do_not_wait_for_a_batch_in_transit(kgo):
+    """kgx_ingest copies its batch to the GPU before it takes the lock that guards the series state, so a scrape that
+    arrives while a large batch is crossing PCIe is served at once from the last completed reduction (the reference's
+    HTTP goroutines never wait for the poll loop's I/O either, main.go:68-74).  One writer thread ingests 1 M-sample
+    batches from pageable memory (milliseconds of copying each); a reader renders on the device all the time
+    (a fraction of a millisecond each): some renders must start AND finish inside a single ingest call, and every
+    body length must be the oracle's after a completed cycle."""
+    import threading
+    import time
+    f = Fleet.config(3)
+    t = f.table(MODE_X)
+    g, o = kgx.Kgx(MODE_X), kgo.Oracle(MODE_X, kgo.JOIN_HASH, min(16, os.cpu_count() or 1))
+    g.set_table(t); o.set_table(t)
+    scrapes = [f.scrape(k) for k in range(4)]
+    want, bodies = set(), []
+    for s in scrapes:  # one window, four cycles
+        o.ingest(s)
+        bodies.append(o.render())
+        want.add(len(bodies[-1]))
+    g.ingest(scrapes[0])
+    assert g.render() == bodies[0]
+    spans, renders, errors, stop = [], [], [], threading.Event()
+
+    def reader():
+        try:
+            while not stop.is_set():
+                t0 = time.perf_counter()
+                n = g.render_device()
+                t1 = time.perf_counter()
+                if n not in want:
+                    errors.append("a body of %d bytes matches no completed cycle" % n)
+                    return
+                renders.append((t0, t1))
+        except Exception as e:  # noqa: BLE001
+            errors.append(repr(e))
+
+    th = threading.Thread(target=reader)
+    th.start()
+    time.sleep(0.05)
+    for s in scrapes[1:]:
+        t0 = time.perf_counter()
+        g.ingest(s)
+        spans.append((t0, time.perf_counter()))
+    stop.set()
+    th.join()
+    assert not errors, errors
+    assert g.render() == bodies[-1]
+    inside = sum(1 for a, b in renders for lo, hi in spans if lo < a and b < hi)
+    assert inside >= 1, "no scrape was served while a batch was in transit (%d renders of ~%.2f ms, ingest calls took %s)" % (
+        len(renders), 1e3 * float(np.mean([b - a for a, b in renders])) if renders else 0.0, ["%.1f ms" % ((hi - lo) * 1e3) for lo, hi in spans])
+
+
 def test_r_staleness_over_cycles(kgo):
     f = Fleet(n_nodes=3, pods=40, procs=300, seed=0xB200 + 5)
     g, o = _pair(kgo, MODE_R_INTENDED)
