@@ -341,27 +341,6 @@ def sharded_leg(cfg, mode, rank, world, dev, local, steps, warmup, barrier, orac
     g1.record()
     barrier()
     gms = fleetshard.max_over_ranks(g0.elapsed_time(g1) / reps, device=dev)
-    # ---- the same concatenation without a collective: every rank writes its body into rank 0's buffer over NVLink
-    p2p_ms = p2p_ok = None
-    try:
-        shared = fleetshard.PeerBuffer(int(offs[-1]), dst=0, device=dev)
-        for _ in range(2):
-            shared.gather_into(body, offs)
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(reps):
-            got = shared.gather_into(body, offs)
-        p2p_ms = fleetshard.max_over_ranks((time.perf_counter() - t0) / reps * 1e3, device=dev)
-        if rank == 0:
-            got.fill_(0)
-        barrier()
-        got = shared.gather_into(body, offs)
-        sums_p = fleetshard.gather_checksums(body)
-        if rank == 0:
-            p2p_ok = bool(fleetshard.verify_gather(got, offs, sums_p))
-        del got, shared
-    except Exception as e:  # noqa: BLE001  (no peer access / IPC on this box: the NCCL gather above stands)
-        p2p_ms, p2p_ok = None, "unavailable: %s" % type(e).__name__
     # ---- parity of what arrived (untimed)
     if rank == 0:
         root_out.fill_(0)
@@ -405,10 +384,6 @@ def sharded_leg(cfg, mode, rank, world, dev, local, steps, warmup, barrier, orac
                           "inbound_gbs": inbound / (gms * 1e-3) / 1e9 if gms > 0 else None,
                           "frac_of_nvlink_inbound_900": inbound / (gms * 1e-3) / 1e9 / 900.0 if gms > 0 else None,
                           "how": "lengths all-gather + one batched group of NCCL send/recv into rank 0's buffer, bodies in node order",
-                          "p2p": {"ms": p2p_ms, "inbound_gbs": inbound / (p2p_ms * 1e-3) / 1e9 if p2p_ms else None,
-                                  "checksums_ok": p2p_ok, "timed": "host clock around copy + stream sync + barrier, max over ranks",
-                                  "how": "rank 0's buffer shared by CUDA IPC; every rank copies its body to its offset (one "
-                                         "device-to-peer cudaMemcpyAsync per rank, all at once), no collective"},
                           "checksums_ok": bool(checks_ok), "oracle_ok": bool(oracle_ok),
                           "oracle_checked": ("whole body" if whole_body_oracle else "%d nodes (first/middle/last of every rank)" % checked),
                           "parity_ok": bool(checks_ok and oracle_ok)}}

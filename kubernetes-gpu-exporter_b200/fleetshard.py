@@ -59,42 +59,6 @@ def gather_bodies(local, dst=0, out=None, group=None):
     return None, offsets
 
 
-class PeerBuffer:
-    """A device buffer on rank `dst` that every rank of the node can write directly: `dst` allocates it and shares its
-    CUDA IPC handle once; the others map it (peer memory over NVLink).  gather_into() then needs no collective: every
-    rank copies its body straight to its offset in the destination buffer, all ranks at once (one cudaMemcpyAsync per
-    rank, device to peer device), and a barrier marks the end.  CUDA only (the gloo tests use gather_bodies)."""
-
-    def __init__(self, nbytes, dst=0, device=None, group=None):
-        from torch.multiprocessing.reductions import reduce_tensor
-        self.dst, self.group, self.rank = dst, group, dist.get_rank(group)
-        box = [None]
-        if self.rank == dst:
-            self.buf = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
-            box[0] = reduce_tensor(self.buf)
-        dist.broadcast_object_list(box, src=dst, group=group)
-        ok = 1
-        if self.rank != dst:
-            try:
-                fn, args = box[0]
-                self.buf = fn(*args)  # the same memory, mapped into this process
-            except Exception:  # noqa: BLE001
-                ok = 0
-        flag = torch.tensor([ok], dtype=torch.int32, device=device)
-        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)  # all ranks agree, or a later barrier would hang
-        if int(flag.item()) == 0:
-            raise RuntimeError("CUDA IPC mapping of the destination buffer failed on some rank")
-
-    def gather_into(self, local, offsets):
-        """Copy this rank's body to offsets[rank] of the shared buffer; returns after all ranks' bytes have landed."""
-        lo = int(offsets[self.rank])
-        if local.numel():
-            self.buf[lo:lo + local.numel()].copy_(local, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        dist.barrier(group=self.group)
-        return self.buf[:int(offsets[-1])] if self.rank == self.dst else None
-
-
 def max_over_ranks(value, device=None, group=None):
     """Device-timed durations are reported as the max over ranks."""
     t = torch.tensor([float(value)], dtype=torch.float64, device=device)
