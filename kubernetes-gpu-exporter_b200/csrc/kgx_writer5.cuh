@@ -181,71 +181,8 @@ __global__ void __launch_bounds__(THREADS, (1280 / THREADS < 32 ? 1280 / THREADS
     mbar_wait(bar, parity);  // the tile's label text has landed (issued during the previous iteration's hand-over)
     parity ^= 1;
     KGX_PC(4);  // header + label wait
-#ifdef KGX_TEAM_EMIT
-    // Four lanes per line: a warp takes its 32 lines in four rounds of eight; lanes 4T..4T+3 stream the line measured by
-    // lane 8r+T, chunk by chunk in turn, so one store instruction writes eight runs of 64 consecutive bytes (about 11
-    // cache lines) instead of 32 chunks in 25 different lines — the scattered 16-byte stores are the busiest thing on
-    // the L1/LSU data pipe.  A lane no longer walks its line from front to back, so every chunk finds its source(s) by
-    // position: which of name | labels | value | next name holds its first byte, and the next one(s) if it straddles.
-    {
-      const uint32_t name_sm = sm0 + lay.names + tile.family * kNameStride + 16;
-      const uint32_t stage0 = sm0 + lay.stage + 32 + s_l0;
-      const uint32_t role = lane & 3, team = lane >> 2;
-      const uint32_t mA = L.off | (uint32_t(L.live) << 24) | (uint32_t(L.first_live) << 25) | (uint32_t(L.last_live) << 26) | (L.vlen << 27);
-      const uint32_t mB = L.lbl_at | (L.vstart << 24);
-      auto gather = [&](uint32_t a) -> uint4 {  // 16 bytes from shared address a (any alignment)
-        const uint32_t wa = a & ~3u, r = (a & 3u) * 8u;
-        const uint32_t w0 = lds32(wa), w1 = lds32(wa + 4), w2 = lds32(wa + 8), w3 = lds32(wa + 12), w4 = lds32(wa + 16);
-        return make_uint4(__funnelshift_r(w0, w1, r), __funnelshift_r(w1, w2, r), __funnelshift_r(w2, w3, r), __funnelshift_r(w3, w4, r));
-      };
-#pragma unroll 1
-      for (uint32_t rnd = 0; rnd < 4; ++rnd) {
-        const int owner = int(rnd * 8 + team);
-        const uint32_t a = __shfl_sync(0xffffffffu, mA, owner), bq = __shfl_sync(0xffffffffu, mB, owner);
-        const uint32_t lbl_len = __shfl_sync(0xffffffffu, L.lbl_len, owner);
-        if (!((a >> 24) & 1u)) continue;  // the line is not printed (no shuffles below: teams may diverge)
-        const bool first_live = (a >> 25) & 1u, last_live = (a >> 26) & 1u;
-        const uint32_t vlen = a >> 27, off = a & 0xffffffu;
-        const uint32_t g = sh + off;
-        const uint32_t b0 = g + name_len, b1 = b0 + lbl_len, b2 = b1 + vlen + 2;
-        const uint32_t start = (g + 15u) & ~15u;
-        const uint32_t stop = last_live ? (b2 & ~15u) : ((b2 + 15u) & ~15u);
-        const uint32_t oslot = sm0 + lay.slots + (k * THREADS + (tid & ~31u) + uint32_t(owner)) * kSlotBytes;
-        const uint32_t d0 = name_sm - g, d1 = stage0 + (bq & 0xffffffu) - b0, d2 = oslot + (bq >> 24) - b1, d3 = name_sm - b2;
-        auto chunk_at = [&](uint32_t p) -> uint4 {  // the 16 output bytes at position p (start <= p, p <= stop)
-          const uint32_t s = uint32_t(p >= b0) + uint32_t(p >= b1) + uint32_t(p >= b2);
-          uint32_t d = s == 0 ? d0 : s == 1 ? d1 : s == 2 ? d2 : d3;
-          uint32_t hi = s == 0 ? b0 : s == 1 ? b1 : s == 2 ? b2 : 0xffffffffu;
-          uint4 v = gather(p + d);
-          if (p + 16 > hi) {                       // straddles into the next source
-            d = s == 0 ? d1 : s == 1 ? d2 : d3;
-            const uint32_t hi2 = s == 0 ? b1 : s == 1 ? b2 : 0xffffffffu;
-            v = merge16(v, gather(p + d), hi - p);
-            if (p + 16 > hi2) {                    // ... and the one after (a value shorter than a chunk)
-              d = s == 0 ? d2 : d3;
-              const uint32_t hi3 = s == 0 ? b2 : 0xffffffffu;
-              v = merge16(v, gather(p + d), hi2 - p);
-              if (p + 16 > hi3) v = merge16(v, gather(p + d3), hi3 - p);
-            }
-          }
-          return v;
-        };
-        if (first_live && role == 0)  // the bytes before the tile's first aligned chunk: nobody else writes them
-          for (uint32_t q = g; q < start && q < b2; ++q) galn[q] = smem[lay.names + tile.family * kNameStride + 16 + (q - g)];
-        for (uint32_t p = start + 16 * role; p < stop; p += 64) stg128_cs(galn + p, chunk_at(p));
-        if (last_live && role == 3 && b2 > stop) {  // the tile ends inside a chunk: its bytes belong to this line
-          s_tail = chunk_at(stop);
-          const uint8_t* sp = reinterpret_cast<const uint8_t*>(&s_tail);
-          for (uint32_t q = 0; q < b2 - stop; ++q) galn[stop + q] = sp[q];
-        }
-      }
-    }
-    if (false) {
-      const uint32_t lbl_src = sm0 + lay.stage + 32 + s_l0 + L.lbl_at;
-#else
     if (L.live) {
       const uint32_t lbl_src = sm0 + lay.stage + 32 + s_l0 + L.lbl_at;
-#endif
       const uint32_t g = sh + L.off;                                                  // first byte of my line (position)
       const uint32_t b0 = g + name_len, b1 = b0 + L.lbl_len, b2 = b1 + L.vlen + 2;    // source boundaries; b2 = line end
       const uint32_t start = (g + 15u) & ~15u;
