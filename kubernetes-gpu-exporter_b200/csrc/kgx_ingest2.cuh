@@ -15,6 +15,7 @@
 #pragma once
 #include "kgx_kernels.cuh"
 #include "kgx_async.cuh"
+#include <type_traits>
 
 namespace kgx {
 
@@ -88,9 +89,8 @@ __global__ void __launch_bounds__(kIngestThreads) k_ingest_nodes(DevTable t, Dev
   const uint32_t tid = threadIdx.x;
   const uint32_t bar = uint32_t(__cvta_generic_to_shared(&s_bar));
   Entry* s_tab = reinterpret_cast<Entry*>(smem);
-  uint32_t* s_slot0 = reinterpret_cast<uint32_t*>(smem + size_t(nm.smem_cells) * sizeof(Entry));
-  uint32_t* s_stride = s_slot0 + nm.smem_pks;
-  uint2* s_bm = reinterpret_cast<uint2*>(s_stride + nm.smem_pks);  // the node's slice of the series index
+  uint2* s_pk = reinterpret_cast<uint2*>(smem + size_t(nm.smem_cells) * sizeof(Entry));  // {first slot, stride} per podkey
+  uint2* s_bm = s_pk + nm.smem_pks;  // the node's slice of the series index
   __shared__ uint32_t s_grank[kMaxStagedGpus];
   if (tid == 0) {
     mbar_init(bar, 1);
@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(kIngestThreads) k_ingest_nodes(DevTable t, Dev
         bulk_g2s(uint32_t(__cvta_generic_to_shared(s_tab)), t.tab + nt.off, nt.cap * uint32_t(sizeof(Entry)), bar);
       }
       if (XMODE)
-        for (uint32_t i = tid; i < K; i += kIngestThreads) { s_slot0[i] = t.pk_slot0[a0 + i]; s_stride[i] = t.pk_stride[a0 + i]; }
+        for (uint32_t i = tid; i < K; i += kIngestThreads) s_pk[i] = make_uint2(t.pk_slot0[a0 + i], t.pk_stride[a0 + i]);
       for (uint32_t i = tid; i < w1 - w0; i += kIngestThreads) s_bm[i] = ix.bm[w0 + i];
       if (XMODE && tid < t.G) s_grank[tid] = t.grank[node * t.G + tid];
       mbar_wait(bar, parity);
@@ -150,6 +150,9 @@ __global__ void __launch_bounds__(kIngestThreads) k_ingest_nodes(DevTable t, Dev
       return w;
     };
     // The trip count is the same for all lanes of a warp (the fold below shuffles): lanes past the end idle.
+    // Two copies of the loop, table in shared or in global memory: the choice is made once per node, not per access.
+    auto rows = [&](auto staged_c) {
+    constexpr bool STAGED = decltype(staged_c)::value;
     Row nxt{};
     if (lo + tid < hi) nxt = load_row(lo + tid);
     for (unsigned long long i = lo + tid; i - (tid & 31) < hi; i += kIngestThreads) {
@@ -164,20 +167,20 @@ __global__ void __launch_bounds__(kIngestThreads) k_ingest_nodes(DevTable t, Dev
         uint32_t pos = uint32_t((uint64_t(dev_hash_pid(pid)) * nt.cap) >> 32);
         bool hit = false;
         for (;;) {
-          const Entry e = staged ? s_tab[pos] : t.tab[nt.off + pos];
+          const Entry e = STAGED ? s_tab[pos] : t.tab[nt.off + pos];
           if (e.val == kEmpty) break;
           if (e.key == pid) {
             hit = true;
             const uint32_t target = e.val & ~kMore;
             uint32_t slot;
             if (XMODE) {
-              const uint32_t gr = staged ? s_grank[gpu] : t.grank[node * t.G + gpu];
-              slot = staged ? s_slot0[target - a0] + gr * s_stride[target - a0] : t.pk_slot0[target] + gr * t.pk_stride[target];
+              if (STAGED) { const uint2 pk = s_pk[target - a0]; slot = pk.x + s_grank[gpu] * pk.y; }
+              else slot = t.pk_slot0[target] + t.grank[node * t.G + gpu] * t.pk_stride[target];
             } else {
               slot = target;
             }
             const uint32_t w = slot >> 5, bit = 1u << (slot & 31);
-            const uint2 bw = staged ? s_bm[w - w0] : ix.bm[w];
+            const uint2 bw = STAGED ? s_bm[w - w0] : ix.bm[w];
             bool fold;
             if (PASS == 0) {
               fold = (bw.x & bit) != 0;
@@ -203,6 +206,8 @@ __global__ void __launch_bounds__(kIngestThreads) k_ingest_nodes(DevTable t, Dev
       }
       if (XMODE) fold_x_warp(acc, r_first, row.used, row.ts, row.sm, row.mem);
     }
+    };
+    if (staged) rows(std::true_type{}); else rows(std::false_type{});
     if (staged) __syncthreads();  // the staging buffer is rewritten for the next node
   }
   if (PASS == 0) {
