@@ -81,44 +81,6 @@ __device__ __forceinline__ void fold_x_warp(const DevAcc& acc, uint32_t r, unsig
   }
 }
 
-#ifdef KGX_FOLD_LOADS
-// Variant of fold_x_warp: only the series rank travels by shuffle; every lane loads the operand of ITS reduction straight
-// from the sample columns (row `wb + src` of the warp's 32 consecutive rows).
-__device__ __forceinline__ void fold_x_warp_loads(const DevAcc& acc, uint32_t r, const DevCols& c, unsigned long long wb) {
-  constexpr uint32_t full = 0xffffffffu;
-  const uint32_t lane = threadIdx.x & 31;
-  if (__all_sync(full, r == kNoRank)) return;
-  uint32_t ra[4], rm[2];
-#pragma unroll
-  for (int g = 0; g < 4; ++g) ra[g] = __shfl_sync(full, r, g * 8 + int(lane >> 2));
-#pragma unroll
-  for (int g = 0; g < 2; ++g) rm[g] = __shfl_sync(full, r, g * 16 + int(lane >> 1));
-  const uint32_t f = lane & 3, f2 = lane & 1;
-  unsigned long long va[4], vm[2];
-#pragma unroll
-  for (int g = 0; g < 4; ++g) {
-    const unsigned long long i = wb + g * 8 + (lane >> 2);
-    va[g] = 1ull;
-    if (ra[g] != kNoRank) {
-      if (f == 1) va[g] = c.used[i];
-      else if (f == 2) va[g] = c.sm_util[i];
-      else if (f == 3) va[g] = c.mem_util[i];
-    }
-  }
-#pragma unroll
-  for (int g = 0; g < 2; ++g) {
-    const unsigned long long i = wb + g * 16 + (lane >> 1);
-    vm[g] = 0;
-    if (rm[g] != kNoRank) vm[g] = f2 ? c.ts_us[i] : c.used[i];
-  }
-#pragma unroll
-  for (int g = 0; g < 4; ++g)
-    if (ra[g] != kNoRank) atomicAdd(acc.xa + size_t(ra[g]) * kXAWords + f, va[g]);
-#pragma unroll
-  for (int g = 0; g < 2; ++g)
-    if (rm[g] != kNoRank) atomicMax(acc.xb + size_t(rm[g]) * kXBWords + f2, vm[g]);
-}
-#endif
 
 template <bool XMODE, int PASS>
 __global__ void __launch_bounds__(kIngestThreads) k_ingest_nodes(DevTable t, DevNodeMeta nm, DevIndex ix, DevAcc acc, DevCols c,
@@ -185,9 +147,7 @@ __global__ void __launch_bounds__(kIngestThreads) k_ingest_nodes(DevTable t, Dev
     auto load_row = [&](unsigned long long i) {
       Row w{};
       w.pid = c.pid[i]; w.gpu = c.gpu[i];
-#ifndef KGX_FOLD_LOADS
       if (XMODE) { w.used = c.used[i]; w.ts = c.ts_us[i]; w.sm = c.sm_util[i]; w.mem = c.mem_util[i]; }
-#endif
       return w;
     };
     // The trip count is the same for all lanes of a warp (the fold below shuffles): lanes past the end idle.
@@ -234,11 +194,7 @@ __global__ void __launch_bounds__(kIngestThreads) k_ingest_nodes(DevTable t, Dev
               if (XMODE) {
                 if (!marked_live) { acc.node_live[node] = 1; marked_live = true; }  // only "non-zero" matters: plain store
                 if (r_first == kNoRank) r_first = r;
-#ifdef KGX_FOLD_LOADS
-                else fold_x_scalar(acc, r, c.used[i], c.ts_us[i], c.sm_util[i], c.mem_util[i]);
-#else
                 else fold_x_scalar(acc, r, row.used, row.ts, row.sm, row.mem);  // the PID sits in several pods' lists
-#endif
               } else {
                 atomicMax(&acc.r_seq[r], (uint64_t(seq) << 32) | uint64_t(i));  // last write in sample order wins
               }
@@ -249,11 +205,7 @@ __global__ void __launch_bounds__(kIngestThreads) k_ingest_nodes(DevTable t, Dev
         }
         if (hit) ++matched; else ++dropped;
       }
-#ifdef KGX_FOLD_LOADS
-      if (XMODE) fold_x_warp_loads(acc, r_first, c, i - (tid & 31));
-#else
       if (XMODE) fold_x_warp(acc, r_first, row.used, row.ts, row.sm, row.mem);
-#endif
     }
     };
     if (staged) rows(std::true_type{}); else rows(std::false_type{});
