@@ -352,6 +352,27 @@ def test_scrapes_do_not_wait_for_a_batch_in_transit(kgo):
         len(renders), 1e3 * float(np.mean([b - a for a, b in renders])) if renders else 0.0, ["%.1f ms" % ((hi - lo) * 1e3) for lo, hi in spans])
 
 
+def test_launch_epoch_wraps_cleanly(kgo):
+    """The writer's look-back words and per-node body offsets carry a 14-bit launch epoch instead of being cleared before
+    every launch, and two tile tickets take turns by the epoch's parity.  Render more often than the epoch can count
+    (16 383): bodies and offsets must stay right across the wrap, with state changes in between."""
+    f = Fleet(n_nodes=3, pods=30, procs=200, seed=0xB200 + 41, scrapes=4)
+    g, o = _pair(kgo, MODE_X)
+    t = f.table(MODE_X)
+    g.set_table(t); o.set_table(t)
+    g.ingest(f.scrape(0)); o.ingest(f.scrape(0))
+    want = _same(g, o)
+    for i in range(16400):
+        n = g.render_device()
+        assert n == len(want), "render %d: %d bytes instead of %d" % (i, n, len(want))
+        if i in (8000, 16380, 16383, 16384, 16390):
+            s = f.scrape(1 + (i % 3))
+            g.ingest(s); o.ingest(s)
+            want = _same(g, o)
+            assert list(g.body_offsets()) == list(o.body_offsets())
+    assert g.render() == want
+
+
 def test_r_staleness_over_cycles(kgo):
     f = Fleet(n_nodes=3, pods=40, procs=300, seed=0xB200 + 5)
     g, o = _pair(kgo, MODE_R_INTENDED)
