@@ -30,7 +30,7 @@ out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_ou
 rows = list(csv.reader(io.StringIO(out)))
 # the page holds one block per captured launch ("Kernel Name" row, header row, one row per instruction): take the
 # first block of the wanted kernel
-want = re.sub(r"I[A-Z].*$", "", kern)  # "k_render3ILi64" (mangled) -> "k_render3"
+want = re.sub(r"I[A-Z].*$", "", kern)  # "k_render5ILi128" (mangled) -> "k_render5"
 k0 = next(i for i, r in enumerate(rows) if r and r[0] == "Kernel Name" and want in r[1])
 h = next(i for i in range(k0, len(rows)) if "Source" in rows[i] and "Address" in rows[i])
 H = rows[h]
