@@ -284,8 +284,11 @@ int kgx_render(kgx_ctx* ctx, uint8_t* out, size_t cap, size_t* len);
  *     beyond that it returns KGX_E_LIMIT and kgx_render must be used.
  *   - `cap` must cover the worst-case body size; if it does not (or d_out is
  *     NULL) it returns KGX_E_NOSPACE with that size in *len.
- *   - The first call on a GPU looks up the array's device address
- *     (cudaGetSymbolAddress); make that first call outside any stream capture.
+ *   - The array's device address is looked up once per GPU
+ *     (cudaGetSymbolAddress, with that GPU current): when the first ctx is
+ *     created on it, or, should that have failed, by the first call here.
+ *     Create the ctx — and to be safe make the first call — outside any
+ *     stream capture.
  *   - All calls, from every ctx on that GPU, share the one array: it is cleared
  *     at the start of each call, and two calls that overlap on the GPU (two
  *     ctxs on different streams) race.  Serialise them. */

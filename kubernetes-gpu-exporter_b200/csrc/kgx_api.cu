@@ -787,6 +787,11 @@ int fetch_body_offsets(kgx_ctx* c) {
 
 }  // namespace
 
+namespace {
+// defined with kgx_render_noalloc at the end of this file: the device address of its in-library scratch array
+int noalloc_scratch(kgx_ctx* c, unsigned long long** out);
+}  // namespace
+
 // =============================== C ABI ========================================
 extern "C" {
 
@@ -819,6 +824,9 @@ int kgx_create(int device, const kgx_opts* opts, kgx_ctx** out) {
       dev_reserve(c, c->d_counters, kCounterWords * 8) != KGX_OK) { kgx_destroy(c); return KGX_E_CUDA; }
   cudaMemsetAsync(c->d_counters.p, 0, kCounterWords * 8, c->stream);
   memset(c->h_counters, 0, C_COUNT * 8);
+  // set-up for kgx_render_noalloc: resolve the scratch array's address on this GPU now (this device is current), so
+  // that the scrape-time call makes no symbol look-up; if it fails here the call itself tries again and reports it
+  { unsigned long long* unused = nullptr; (void)noalloc_scratch(c, &unused); tl_err.clear(); }
   *out = c;
   return KGX_OK;
 }
