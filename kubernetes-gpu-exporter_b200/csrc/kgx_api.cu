@@ -572,8 +572,6 @@ int set_table_device(kgx_ctx* c, const kgx_table* t, CarriedDev* carried) {
   return KGX_OK;
 }
 
-// Launch one pass of the join over the batch `dc` (PASS 0: steady state; PASS 1: after an index rebuild, folds exactly
-// the matches pass 0 had to skip).
 // A pending window reset, carried out on its own (the next call is not a node-grouped join that could fold it in).
 int flush_reset(kgx_ctx* c) {
   if (!c->reset_pending) return KGX_OK;
@@ -595,6 +593,8 @@ uint32_t ingest_parts(const kgx_ctx* c, uint64_t n_rows) {
   return uint32_t(std::min<uint64_t>(std::min<uint64_t>(by_rows, ctas / c->plan.n_nodes), 64));
 }
 
+// Launch one pass of the join over the batch `dc` (PASS 0: steady state; PASS 1: after an index rebuild, folds exactly
+// the matches pass 0 had to skip).  `reset`: a window reset is folded into this pass (node-grouped X-mode batches only).
 void launch_ingest_pass(kgx_ctx* c, const DevCols& dc, bool grouped, int pass, bool reset = false) {
   const Plan& p = c->plan;
   const bool x = c->mode == KGX_MODE_X;
@@ -648,8 +648,8 @@ int handle_churn(kgx_ctx* c) {
   return launch_finalize_r(c, c->pending_cols, c->pending_grouped);
 }
 
-// Statistics and churn check of the latest join (queued by ingest_device_locked): wait for it, read what its last
-// CTA posted to mapped host memory, and run the churn path if it saw new series.
+// Statistics and churn check of the latest join (queued by ingest_device_locked): wait for it, read what the hand-over
+// kernel behind it posted to mapped host memory, and run the churn path if it saw new series.
 int settle_ingest(kgx_ctx* c) {
   if (!c->ingest_pending) return KGX_OK;
   KGX_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -683,9 +683,7 @@ int ingest_device_locked(kgx_ctx* c, const kgx_cols* s) {
   const bool grouped = s->node_off != nullptr && !getenv("KGX_INGEST_V1");
   {
     Timed tm(c, KGX_K_INGEST);
-    // the statistics reach mapped host memory by a store of the kernel's last CTA, not by a D2H copy: a copy would
-    // queue on the device->host copy engine behind a body that kgx_render_begin may still be sending (tens of ms)
-    // the join clears each node as it takes it — if one CTA owns the node
+    // a pending window reset: the join clears each node as it takes it — if one CTA owns the node
     const bool fold_reset = c->reset_pending && x && grouped && s->n && c->n_series && ingest_parts(c, s->n) == 1;
     if (!fold_reset) KGX_TRY(flush_reset(c));
     c->reset_pending = false;
@@ -694,7 +692,9 @@ int ingest_device_locked(kgx_ctx* c, const kgx_cols* s) {
     tm.launches(1);
     KGX_TRY(launch_check(c, "k_ingest"));
   }
-  bool handed_over = false;  // R modes: k_finalize_r posts the statistics too
+  // The statistics reach mapped host memory by a store of a kernel queued behind the join, not by a D2H copy: a copy
+  // would queue on the device->host copy engine behind a body that kgx_render_begin may still be sending (tens of ms).
+  bool handed_over = false;  // R modes: k_finalize_r posts them too
   KGX_TRY(launch_finalize_r(c, dc, grouped, true, &handed_over));
   if (s->n && !handed_over) {
     Timed tm(c, KGX_K_INGEST);
