@@ -139,8 +139,8 @@ __global__ void __launch_bounds__(THREADS, (1280 / THREADS < 32 ? 1280 / THREADS
     if (t > 0) {
       // One step covers 32 * kLookBack5 predecessors: kLookBack5 coalesced loads of 32 consecutive look-back words each
       // (lane 0 of load 0 is the direct predecessor), all in flight together.  The predecessors' sizes were published a
-      // tile period ago, so nothing here spins; what costs is the WALK back to the nearest tile that already knows its
-      // prefix — hundreds of tickets with thousands of tiles in flight, ~18 dependent L2 round trips at 32 per step.
+      // tile period ago, so the walk rarely spins; steps wider than 32 words measured slower (1.51 / 1.53 / 1.67 ms at
+      // 1 / 4 / 8 words per lane), so kLookBack5 is 1.
       long long p = (long long)t - 1 - lane;
       for (;;) {
         unsigned long long st[kLookBack5];
