@@ -39,7 +39,9 @@
 extern "C" {
 #endif
 
-#define KGX_ABI_VERSION 1
+/* 2: kgx_ingest_device returns with the join in flight; kgx_last_error is per calling thread; kgx_body_node and
+ *    kgx_read_labels added.  Struct layouts are those of version 1. */
+#define KGX_ABI_VERSION 2
 
 /* ---- error codes -------------------------------------------------------- */
 #define KGX_OK 0

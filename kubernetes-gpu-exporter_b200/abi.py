@@ -5,7 +5,7 @@ import ctypes as C
 
 import numpy as np
 
-KGX_ABI_VERSION = 1
+KGX_ABI_VERSION = 2
 KGX_OK, KGX_E_INVAL, KGX_E_NOMEM, KGX_E_CUDA, KGX_E_NOSPACE, KGX_E_STATE, KGX_E_LIMIT = 0, -1, -2, -3, -4, -5, -6
 MODE_R_INTENDED, MODE_R_LITERAL, MODE_X = 0, 1, 2
 K_INGEST, K_FINALIZE, K_INDEX, K_RENDER, K_OTHER, K_COUNT = 0, 1, 2, 3, 4, 5
