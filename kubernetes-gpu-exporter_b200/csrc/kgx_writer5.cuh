@@ -34,10 +34,11 @@ struct LineState {  // what MEASURE leaves for EMIT, per thread
   bool live, first_live, last_live;
 };
 
-// 1 280 resident threads per SM is what shared memory allows with 128-line tiles (10 CTAs): the register budget is
-// pinned to that (48 per thread), or two more registers would cost a whole CTA per SM.
+// Shared memory allows 10 CTAs of 128 lines per SM, but pinning the register budget to that (48 per thread) costs a
+// spill and measured slower than the 56 registers the kernel wants at 9 CTAs: 1.420 vs 1.382 ms (64 registers at 8 CTAs:
+// 1.423 ms).  So: 1 152 resident threads.
 template <int THREADS>
-__global__ void __launch_bounds__(THREADS, (1280 / THREADS < 32 ? 1280 / THREADS : 32)) k_render5(DevRender R, RenderLayout lay, DevAcc acc, unsigned long long* counters) {
+__global__ void __launch_bounds__(THREADS, (1152 / THREADS < 32 ? 1152 / THREADS : 32)) k_render5(DevRender R, RenderLayout lay, DevAcc acc, unsigned long long* counters) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ unsigned long long s_scan[THREADS / 32];
   __shared__ uint4 s_tail;
