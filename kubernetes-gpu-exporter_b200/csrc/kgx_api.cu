@@ -89,6 +89,12 @@ struct kgx_ctx {
   int render_grid = 0, render_threads = 128;  // measured best on B200: direct stores, 128-line tiles
   size_t last_len = 0;
   bool rendered = false;
+  // Small configurations (one node, a few hundred processes) are bound by calls into the driver, not by bytes: a batch
+  // whose columns fit kSmallBytes crosses in ONE copy from a pinned staging buffer, and a body whose upper bound fits
+  // leaves in one copy queued right behind the writer (no second synchronisation).
+  uint64_t out_bound = 0;          // upper bound of the body size (what d_out holds)
+  uint8_t *h_small_in = nullptr, *h_small_out = nullptr;  // pinned, kSmallBytes each, allocated on first use
+  DBuf d_small_in;
   std::vector<uint64_t> body_off;  // host copy of the last body's per-node offsets (kgx_body_node), fetched on first use
   bool body_off_valid = false;
   std::vector<FamMeta> fam;
@@ -113,6 +119,7 @@ struct kgx_ctx {
 
 namespace {
 
+constexpr size_t kSmallBytes = 256 << 10;
 constexpr int kCounterWords = 16;  // C_COUNT words the kernels know + two scratch words for kgx_expire
 constexpr int kExpireWords = 8;
 
@@ -368,6 +375,7 @@ int rebuild_index(kgx_ctx* c) {
   for (const FamMeta& m : c->fam)
     cap += uint64_t(S) * (m.name_len + 2 + kMaxValueText) + lbl_total + uint64_t(NN) * m.header_len;
   KGX_TRY(dev_reserve(c, c->d_out, size_t(cap)));
+  c->out_bound = cap;
   KGX_CUDA(c, cudaStreamSynchronize(c->stream));
   c->stats.rebuilds += 1;
   return KGX_OK;
@@ -735,7 +743,17 @@ int launch_render(kgx_ctx* c, uint8_t* out, bool guard) {
   return launch_check(c, "k_render");
 }
 
-int render_device_locked(kgx_ctx* c, size_t* len, bool keep_copies = false) {
+// `h_copy` (pinned, `h_cap` bytes): also queue the copy of the body's upper bound right behind the writer, so that a
+// small body needs no second synchronisation; *copied = bytes that copy covered (0: none).
+int render_device_locked(kgx_ctx* c, size_t* len, bool keep_copies = false, uint8_t* h_copy = nullptr, size_t h_cap = 0,
+                         size_t* copied = nullptr) {
+  if (copied) *copied = 0;
+  auto queue_copy = [&]() -> int {
+    if (!h_copy || c->out_bound == 0 || c->out_bound > h_cap) { if (copied) *copied = 0; return KGX_OK; }
+    KGX_CUDA(c, cudaMemcpyAsync(h_copy, c->d_out.p, size_t(c->out_bound), cudaMemcpyDeviceToHost, c->stream));
+    if (copied) *copied = size_t(c->out_bound);
+    return KGX_OK;
+  };
   if (!keep_copies) wait_copy(c);
   c->body_off_valid = false;
   // a scrape may arrive before the first poll cycle (the reference starts its HTTP server first, main.go:68-74):
@@ -749,6 +767,7 @@ int render_device_locked(kgx_ctx* c, size_t* len, bool keep_copies = false) {
   // runs here before a second launch.  Steady state: two kernels, one synchronisation.
   const bool guard = c->ingest_pending;
   KGX_TRY(launch_render(c, ptr<uint8_t>(c->d_out), guard));
+  KGX_TRY(queue_copy());
   KGX_CUDA(c, cudaStreamSynchronize(c->stream));
   if (guard) {
     c->ingest_pending = false;
@@ -757,6 +776,7 @@ int render_device_locked(kgx_ctx* c, size_t* len, bool keep_copies = false) {
     if (c->h_counters[C_NEW]) {
       KGX_TRY(handle_churn(c));
       KGX_TRY(launch_render(c, ptr<uint8_t>(c->d_out), false));
+      KGX_TRY(queue_copy());
       KGX_CUDA(c, cudaStreamSynchronize(c->stream));
     }
   }
@@ -842,6 +862,9 @@ void kgx_destroy(kgx_ctx* c) {
   for (auto& b : c->d_tmp) dev_free(c, b);
   for (auto& r : c->regions) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
   if (c->h_counters) cudaFreeHost(c->h_counters);
+  if (c->h_small_in) cudaFreeHost(c->h_small_in);
+  if (c->h_small_out) cudaFreeHost(c->h_small_out);
+  dev_free(c, c->d_small_in);
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->in_stream) cudaStreamDestroy(c->in_stream);
   if (c->ev_rendered) cudaEventDestroy(c->ev_rendered);
@@ -976,12 +999,30 @@ int kgx_ingest(kgx_ctx* c, const kgx_cols* cols) {
   const void* src[9] = {cols->pid, cols->gpu, cols->used, cols->node, cols->sm_util, cols->mem_util, cols->ts_us, cols->node_off, cols->gpu_total};
   const size_t bytes[9] = {n * 4, n * 4, n * 8, n * 4, n * 4, n * 4, n * 8, (size_t(NN) + 1) * 8, size_t(NN) * G * 8};
   const void* dst[9];
-  for (int k = 0; k < 9; ++k) {
-    dst[k] = nullptr;
-    if (!src[k]) continue;
-    KGX_TRY(dev_reserve(c, c->d_cols[k], bytes[k]));
-    if (bytes[k]) KGX_CUDA(c, cudaMemcpyAsync(c->d_cols[k].p, src[k], bytes[k], cudaMemcpyHostToDevice, c->in_stream));
-    dst[k] = c->d_cols[k].p;
+  size_t packed = 0, at[9];
+  for (int k = 0; k < 9; ++k) { at[k] = packed; if (src[k]) packed += (bytes[k] + 15) & ~size_t(15); }
+  if (packed <= kSmallBytes && !c->h_small_in &&
+      cudaHostAlloc(reinterpret_cast<void**>(&c->h_small_in), kSmallBytes, cudaHostAllocDefault) != cudaSuccess) {
+    c->h_small_in = nullptr;
+    cudaGetLastError();
+  }
+  if (packed <= kSmallBytes && c->h_small_in) {  // a small batch: pack the columns, one copy instead of nine
+    KGX_TRY(dev_reserve(c, c->d_small_in, kSmallBytes));
+    for (int k = 0; k < 9; ++k) {
+      dst[k] = nullptr;
+      if (!src[k]) continue;
+      if (bytes[k]) memcpy(c->h_small_in + at[k], src[k], bytes[k]);
+      dst[k] = static_cast<uint8_t*>(c->d_small_in.p) + at[k];
+    }
+    if (packed) KGX_CUDA(c, cudaMemcpyAsync(c->d_small_in.p, c->h_small_in, packed, cudaMemcpyHostToDevice, c->in_stream));
+  } else {
+    for (int k = 0; k < 9; ++k) {
+      dst[k] = nullptr;
+      if (!src[k]) continue;
+      KGX_TRY(dev_reserve(c, c->d_cols[k], bytes[k]));
+      if (bytes[k]) KGX_CUDA(c, cudaMemcpyAsync(c->d_cols[k].p, src[k], bytes[k], cudaMemcpyHostToDevice, c->in_stream));
+      dst[k] = c->d_cols[k].p;
+    }
   }
   KGX_CUDA(c, cudaStreamSynchronize(c->in_stream));  // the caller's buffers are free from here on
   d.pid = static_cast<const uint32_t*>(dst[0]); d.gpu = static_cast<const uint32_t*>(dst[1]);
@@ -1143,12 +1184,21 @@ int kgx_render(kgx_ctx* c, uint8_t* out, size_t cap, size_t* len) {
   if (!c || !len) return KGX_E_INVAL;
   std::lock_guard<std::mutex> g(c->mu);
   cudaSetDevice(c->device);
-  KGX_TRY(render_device_locked(c, len));
+  if (!c->h_small_out && cudaHostAlloc(reinterpret_cast<void**>(&c->h_small_out), kSmallBytes, cudaHostAllocDefault) != cudaSuccess) {
+    c->h_small_out = nullptr;
+    cudaGetLastError();  // no pinned memory: the two-step path below serves every size
+  }
+  size_t copied = 0;
+  KGX_TRY(render_device_locked(c, len, false, c->h_small_out, kSmallBytes, &copied));
   if (*len > cap) return fail(c, KGX_E_NOSPACE, "output buffer too small");
   if (*len) {
     if (!out) return fail(c, KGX_E_INVAL, "null output buffer");
-    KGX_CUDA(c, cudaMemcpyAsync(out, c->d_out.p, *len, cudaMemcpyDeviceToHost, c->stream));
-    KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (*len <= copied) {  // a small body: it arrived with the writer's own synchronisation
+      memcpy(out, c->h_small_out, *len);
+    } else {
+      KGX_CUDA(c, cudaMemcpyAsync(out, c->d_out.p, *len, cudaMemcpyDeviceToHost, c->stream));
+      KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
   }
   return KGX_OK;
 }

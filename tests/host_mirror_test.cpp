@@ -69,9 +69,50 @@ static int big_collect() {
   return 0;
 }
 
+// One node at BASELINE config 1's size (64 pods, 256 processes) through the C ABI without an interpreter in the way:
+// what one poll + scrape costs when the step is launch-bound.  Prints microseconds per call pair.
+static int small_latency() {
+  const uint64_t GiB = 1ull << 30;
+  Exporter ex(0, false);
+  kgx_ctx* c = ex.ctx();
+  PodPIDMap m;
+  std::vector<Device> devs(8);
+  uint32_t pid = 1000;
+  for (uint32_t p = 0; p < 64; ++p)
+    for (uint32_t k = 0; k < 4; ++k, ++pid) {
+      m["pod-" + std::to_string(p)].push_back(std::to_string(pid));
+      devs[pid % 8].processInfos.push_back(ProcessInfo{pid, (uint64_t(pid) % 4096 + 1) * (2ull << 20)});
+    }
+  for (Device& d : devs) d.memoryInfo.Total = 192 * GiB;
+  ex.Cycle(m, devs);  // installs the table, first ingest
+  std::vector<uint32_t> pids, gpus;
+  std::vector<uint64_t> used, total(8, 192 * GiB);
+  for (size_t di = 0; di < devs.size(); ++di)
+    for (const ProcessInfo& p : devs[di].processInfos) { pids.push_back(p.Pid); gpus.push_back(uint32_t(di)); used.push_back(p.UsedGpuMemory); }
+  kgx_cols cols{};
+  cols.n = pids.size(); cols.pid = pids.data(); cols.gpu = gpus.data(); cols.used = used.data(); cols.gpu_total = total.data();
+  std::vector<uint8_t> body(1 << 20);
+  size_t len = 0;
+  for (int i = 0; i < 200; ++i) { CHECK(kgx_ingest(c, &cols) == KGX_OK); CHECK(kgx_render(c, body.data(), body.size(), &len) == KGX_OK); }
+  const int reps = 2000;
+  const auto t0 = std::chrono::steady_clock::now();
+  for (int i = 0; i < reps; ++i) { kgx_ingest(c, &cols); kgx_render(c, body.data(), body.size(), &len); }
+  const auto t1 = std::chrono::steady_clock::now();
+  for (int i = 0; i < reps; ++i) kgx_render(c, body.data(), body.size(), &len);
+  const auto t2 = std::chrono::steady_clock::now();
+  const double pair_us = std::chrono::duration<double, std::micro>(t1 - t0).count() / reps;
+  const double render_us = std::chrono::duration<double, std::micro>(t2 - t1).count() / reps;
+  std::printf("256 samples, %zu bytes of text: kgx_ingest + kgx_render %.1f us per cycle, kgx_render alone %.1f us (host buffers, C++ caller)\n",
+              len, pair_us, render_us);
+  CHECK(len > 30000 && pair_us < 2000.0);
+  std::puts("ok");
+  return 0;
+}
+
 int main(int argc, char** argv) {
   if (argc < 2) return 2;
   if (std::string(argv[1]) == "big") return big_collect();
+  if (std::string(argv[1]) == "small") return small_latency();
   std::ifstream f(argv[1], std::ios::binary);
   std::stringstream golden;
   golden << f.rdbuf();

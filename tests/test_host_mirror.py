@@ -39,3 +39,13 @@ def test_host_mirror_collects_a_million_series_in_bulk(tmp_path):
     r = subprocess.run([exe, "big"], capture_output=True, text=True, timeout=300)
     print(r.stdout)
     assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_host_mirror_small_config_latency(tmp_path):
+    """BASELINE config 1's size through the C ABI from C++ (no interpreter in the timed loop): prints the cost of one
+    poll + scrape when the step is launch-bound."""
+    exe = _compile(tmp_path)
+    r = subprocess.run([exe, "small"], capture_output=True, text=True, timeout=120)
+    print(r.stdout)
+    assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout + r.stderr
