@@ -123,3 +123,31 @@ func Handler(ctx *Ctx, fallback http.Handler) http.Handler {
 		pool.Put(bp)
 	})
 }
+
+// StreamingHandler serves the same bytes as Handler with chunked transfer
+// encoding (net/http switches to it by itself when no Content-Length is set and
+// the body outgrows its buffer): the body stays in device memory and crosses
+// `chunkBytes` at a time, so a fleet-sized body (gigabytes) needs one chunk of
+// host memory and its first bytes are on the wire after one render and one
+// chunk copy.  One scrape at a time (the body on the device belongs to the
+// scrape being served), like promhttp's MaxRequestsInFlight = 1; a second
+// scrape waits.
+func StreamingHandler(ctx *Ctx, fallback http.Handler, chunkBytes int) http.Handler {
+	var mu sync.Mutex
+	chunk := make([]byte, chunkBytes)
+	return http.HandlerFunc(func(w http.ResponseWriter, r *http.Request) {
+		ct := expfmt.Negotiate(r.Header)
+		if ct.FormatType() != expfmt.TypeTextPlain {
+			fallback.ServeHTTP(w, r)
+			return
+		}
+		mu.Lock()
+		defer mu.Unlock()
+		w.Header().Set("Content-Type", string(ct))
+		if n, err := ctx.WriteBodyTo(w, chunk); err != nil && n == 0 {
+			// nothing written yet: the header is still ours (promhttp.HandlerOpts{} default: HTTP 500)
+			w.Header().Del("Content-Type")
+			http.Error(w, err.Error(), http.StatusInternalServerError)
+		}
+	})
+}

@@ -15,6 +15,7 @@ import "C"
 
 import (
 	"fmt"
+	"io"
 	"runtime"
 	"unsafe"
 )
@@ -204,6 +205,38 @@ func (c *Ctx) Render(buf []byte) ([]byte, error) {
 			return nil, err
 		}
 		return buf[:int(n)], nil
+	}
+}
+
+// RenderDevice renders into device memory and returns the size of the body.
+func (c *Ctx) RenderDevice() (int, error) {
+	var n C.size_t
+	rc := C.kgx_render_device(c.p, &n)
+	return int(n), c.err(rc)
+}
+
+// WriteBodyTo renders on the device and writes the body to w chunk by chunk
+// (len(chunk) bytes at a time, chunk reused): host memory stays at one chunk
+// whatever the size of the body, and the first bytes leave one render and one
+// chunk copy after the call.  The caller serialises scrapes on this Ctx.
+func (c *Ctx) WriteBodyTo(w io.Writer, chunk []byte) (int64, error) {
+	if _, err := c.RenderDevice(); err != nil {
+		return 0, err
+	}
+	var at int64
+	for {
+		var n C.size_t
+		rc := C.kgx_body_read(c.p, C.uint64_t(at), (*C.uint8_t)(unsafe.Pointer(&chunk[0])), C.size_t(len(chunk)), &n)
+		if err := c.err(rc); err != nil {
+			return at, err
+		}
+		if n == 0 {
+			return at, nil
+		}
+		if _, err := w.Write(chunk[:int(n)]); err != nil {
+			return at, err
+		}
+		at += int64(n)
 	}
 }
 

@@ -329,6 +329,19 @@ int kgx_body_offsets(kgx_ctx* ctx, uint64_t* off, size_t n);
  * cap is too small.  The body stays valid until the next render on this ctx. */
 int kgx_body_node(kgx_ctx* ctx, uint32_t node, uint8_t* out, size_t cap, size_t* len);
 
+/* A byte range of the last rendered text, copied to host memory `out`: up to
+ * `cap` bytes from `offset`; *n receives how many were copied (0 at the end of
+ * the body).  For a handler that streams the body with chunked transfer
+ * encoding instead of holding all of it in host memory: kgx_render_device,
+ * then kgx_body_read chunk after chunk into the http.ResponseWriter (what
+ * promhttp does with its pooled buffer behind main.go:69-71).
+ * The first chunk is out one render and one chunk copy after the scrape
+ * arrived, whatever the body's size.  KGX_E_STATE before any render,
+ * KGX_E_INVAL if offset lies beyond the body.  The body stays valid until the
+ * next render on this ctx and no lock is held between calls: the handler
+ * serialises its scrapes (promhttp's MaxRequestsInFlight = 1 does the same). */
+int kgx_body_read(kgx_ctx* ctx, uint64_t offset, uint8_t* out, size_t cap, size_t* n);
+
 /* ---- Collector read-back (prometheus.Collector.Collect) ------------------ */
 
 /* Values of family `family` (index in sorted family order) for every series

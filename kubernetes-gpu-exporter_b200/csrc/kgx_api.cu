@@ -1290,6 +1290,23 @@ int kgx_body_node(kgx_ctx* c, uint32_t node, uint8_t* out, size_t cap, size_t* l
   return KGX_OK;
 }
 
+int kgx_body_read(kgx_ctx* c, uint64_t offset, uint8_t* out, size_t cap, size_t* n) {
+  if (!c || !n) return KGX_E_INVAL;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  *n = 0;
+  if (!c->rendered) return fail(c, KGX_E_STATE, "no rendered body");
+  if (offset > c->last_len) return fail(c, KGX_E_INVAL, "offset beyond the end of the body");
+  const size_t take = size_t(std::min<uint64_t>(cap, c->last_len - offset));
+  if (take) {
+    if (!out) return fail(c, KGX_E_INVAL, "null output buffer");
+    KGX_CUDA(c, cudaMemcpyAsync(out, ptr<uint8_t>(c->d_out) + offset, take, cudaMemcpyDeviceToHost, c->stream));
+    KGX_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
+  *n = take;
+  return KGX_OK;
+}
+
 int kgx_family_count(kgx_ctx* c) { return c ? int(c->fam.size()) : KGX_E_INVAL; }
 
 int kgx_family_info(kgx_ctx* c, int family, const char** name, const char** help, const char* const** names, int* n_labels) {

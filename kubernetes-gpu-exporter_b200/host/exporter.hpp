@@ -134,6 +134,22 @@ class Exporter {
     return Response{200, "text/plain; version=0.0.4; charset=utf-8; escaping=values", buf_.substr(0, len)};
   }
 
+  // GET /metrics with chunked transfer encoding: the body stays on the device and is handed to `write` one chunk at a
+  // time (Go side: StreamingHandler in go/kgx/collector.go).  Returns the status code; 500 only before the first chunk.
+  template <class Write>
+  int ServeHTTPChunked(size_t chunk_bytes, Write&& write) {
+    size_t len = 0;
+    if (kgx_render_device(ctx_, &len) != KGX_OK) return 500;
+    if (chunk_.size() < chunk_bytes) chunk_.resize(chunk_bytes);
+    for (uint64_t at = 0;;) {
+      size_t n = 0;
+      if (kgx_body_read(ctx_, at, reinterpret_cast<uint8_t*>(&chunk_[0]), chunk_bytes, &n) != KGX_OK) return at ? 200 : 500;
+      if (n == 0) return 200;
+      write(chunk_.data(), n);
+      at += n;
+    }
+  }
+
   kgx_ctx* ctx() { return ctx_; }
 
  private:
@@ -160,6 +176,7 @@ class Exporter {
   bool literal_ = false;
   std::vector<Desc> descs_;
   std::string buf_ = std::string(1 << 16, '\0');
+  std::string chunk_;
 };
 
 }  // namespace kgx_host

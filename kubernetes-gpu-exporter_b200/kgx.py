@@ -15,7 +15,7 @@ _LIB = None
 
 EXPORTS = [
     "kgx_abi_version", "kgx_strerror", "kgx_last_error", "kgx_create", "kgx_destroy", "kgx_set_table", "kgx_ingest",
-    "kgx_ingest_device", "kgx_ingest_nvml", "kgx_ingest_nvml_x", "kgx_reset_window", "kgx_expire", "kgx_render_device", "kgx_render", "kgx_render_begin", "kgx_render_end", "kgx_body_device", "kgx_body_offsets", "kgx_body_node",
+    "kgx_ingest_device", "kgx_ingest_nvml", "kgx_ingest_nvml_x", "kgx_reset_window", "kgx_expire", "kgx_render_device", "kgx_render", "kgx_render_begin", "kgx_render_end", "kgx_body_device", "kgx_body_offsets", "kgx_body_node", "kgx_body_read",
     "kgx_read_values", "kgx_read_labels", "kgx_render_noalloc", "kgx_family_count", "kgx_family_info", "kgx_slot_labels", "kgx_format_values", "kgx_host_alloc",
     "kgx_host_free", "kgx_get_stats", "kgx_get_profile", "kgx_profile_reset", "kgx_set_profile", "kgx_sync",
 ]
@@ -55,6 +55,7 @@ def lib():
         L.kgx_body_device.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]
         L.kgx_body_offsets.argtypes = [vp, abi.u64p, C.c_size_t]
         L.kgx_body_node.argtypes = [vp, C.c_uint32, vp, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.kgx_body_read.argtypes = [vp, C.c_uint64, vp, C.c_size_t, C.POINTER(C.c_size_t)]
         L.kgx_read_labels.argtypes = [vp, vp, C.c_size_t, abi.u64p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]
         L.kgx_render_noalloc.argtypes = [vp, vp, C.c_size_t, C.POINTER(C.c_size_t)]
         L.kgx_read_values.argtypes = [vp, C.c_int, C.POINTER(C.c_double), abi.u32p, C.c_size_t, C.POINTER(C.c_size_t)]
@@ -219,6 +220,25 @@ class Kgx:
         out = np.empty(max(1, n.value), dtype=np.uint8)
         self._chk(lib().kgx_body_node(self._h, int(node), out.ctypes.data, out.nbytes, C.byref(n)))
         return out[:n.value].tobytes()
+
+    def body_read(self, offset, out):
+        """Up to len(out) bytes of the last rendered text from `offset` into the uint8 array `out` (kgx_body_read);
+        returns how many were copied (0 at the end of the body)."""
+        n = C.c_size_t()
+        self._chk(lib().kgx_body_read(self._h, int(offset), out.ctypes.data, out.nbytes, C.byref(n)))
+        return n.value
+
+    def stream_body(self, chunk_bytes=1 << 20):
+        """Render on the device, then yield the body chunk by chunk (what a chunked-transfer handler writes)."""
+        self.render_device()
+        buf = np.empty(chunk_bytes, dtype=np.uint8)
+        at = 0
+        while True:
+            n = self.body_read(at, buf)
+            if n == 0:
+                return
+            yield buf[:n].tobytes()
+            at += n
 
     def family_count(self):
         return lib().kgx_family_count(self._h)

@@ -147,6 +147,12 @@ int main(int argc, char** argv) {
   r = ex.ServeHTTP();
   CHECK(r.body.find("pod_gpu_memory_usage{pid=\"4242\",pod=\"trainer-0\"} 1.073741824e+09\n") != std::string::npos);
   CHECK(r.body.find("pod_gpu_memory_usage{pid=\"7\",pod=\"web \\\"a\\\"\"} 200\n") != std::string::npos);
+  {  // the same scrape served with chunked transfer encoding, 7 bytes at a time: the same bytes
+    std::string chunked;
+    int n_chunks = 0;
+    CHECK(ex.ServeHTTPChunked(7, [&](const char* p, size_t n) { chunked.append(p, n); ++n_chunks; }) == 200);
+    CHECK(chunked == r.body && n_chunks == int((r.body.size() + 6) / 7));
+  }
 
   // the predicate exactly as written at main.go:144-145
   Exporter lit(0, /*literal=*/true);

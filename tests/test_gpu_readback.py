@@ -65,6 +65,38 @@ def test_body_node_is_the_nodes_slice(kgo, mode):
     assert rc == abi.KGX_E_NOSPACE and n.value == int(off[1] - off[0])
 
 
+def test_body_read_streams_the_same_bytes(kgo):
+    """kgx_body_read: the body chunk by chunk (a chunked-transfer handler) equals kgx_render's, for chunk sizes that do
+    and do not divide it; ranges, the end of the body and the error cases."""
+    f = Fleet(n_nodes=11, pods=50, procs=400, seed=0xB200 + 23)
+    t = f.table(MODE_X)
+    g, o = kgx.Kgx(MODE_X), kgo.Oracle(MODE_X, kgo.JOIN_HASH, 2)
+    g.set_table(t); o.set_table(t)
+    buf = np.zeros(64, dtype=np.uint8)
+    with pytest.raises(kgx.KgxError) as e:      # nothing rendered yet
+        g.body_read(0, buf)
+    assert e.value.code == abi.KGX_E_STATE
+    s = f.scrape(0)
+    g.ingest(s); o.ingest(s)
+    want = o.render()
+    assert g.render() == want
+    for chunk in (1 << 20, 4096, 1000, len(want), len(want) - 1):
+        parts = list(g.stream_body(chunk))
+        assert b"".join(parts) == want
+        assert len(parts) == (len(want) + chunk - 1) // chunk and all(len(p) == chunk for p in parts[:-1])
+    mid = len(want) // 3
+    assert g.body_read(mid, buf) == 64 and buf.tobytes() == want[mid:mid + 64]
+    assert g.body_read(len(want) - 10, buf) == 10 and buf[:10].tobytes() == want[-10:]
+    assert g.body_read(len(want), buf) == 0       # the end: no bytes, no error
+    with pytest.raises(kgx.KgxError) as e:
+        g.body_read(len(want) + 1, buf)
+    assert e.value.code == abi.KGX_E_INVAL
+    g.reset_window(); o.reset_window()            # the next scrape: the reader sees the new body
+    s = f.scrape(1)
+    g.ingest(s); o.ingest(s)
+    assert b"".join(g.stream_body(8192)) == o.render()
+
+
 @pytest.mark.parametrize("mode", [MODE_R_INTENDED, MODE_X])
 def test_read_labels_in_one_call(kgo, mode):
     f = Fleet(n_nodes=9, pods=60, procs=500, seed=0xB200 + 22)
