@@ -9,9 +9,9 @@
 //
 //   iteration i:   MEASURE tile t(i+1)   state loads, value text into the other slot buffer, CTA scan,
 //                                        size published                     <- a whole tile period early
-//                  EMIT    tile t(i)     look-back (the predecessors' sizes have been out for a period), header,
-//                                        stream the lines
-//                  hand-over             labels of t(i+1) -> stage (TMA), ticket + descriptor of t(i+2)
+//                  EMIT    tile t(i)     look-back (the predecessors' sizes have been out for a period), ticket of
+//                                        t(i+2) drawn, header, lines streamed; thread 0 then loads t(i+2)'s descriptor
+//                  one CTA barrier       then labels of t(i+1) -> stage (TMA)
 //
 // Tickets are still drawn in output order and sizes are still published in ticket order, so the look-back never waits
 // on a tile that has not started; it just no longer waits on one that is still formatting.
@@ -43,9 +43,8 @@ __global__ void __launch_bounds__(THREADS, (1152 / THREADS < 32 ? 1152 / THREADS
   __shared__ unsigned long long s_scan[THREADS / 32];
   __shared__ uint4 s_tail;
   __shared__ __align__(8) unsigned long long s_bar;
-  __shared__ uint32_t s_tk[2];   // tickets of the two tiles in flight
-  __shared__ Tile s_desc[2];     // their descriptors
-  __shared__ uint32_t s_l0;      // where the first label starts inside the staged range (tile being emitted)
+  __shared__ uint32_t s_tk[3];   // tickets of the tile being emitted, the one being measured and the one after
+  __shared__ Tile s_desc[3];     // their descriptors
   const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   unsigned long long* ticket = ticket_of(counters, R.epoch);
   if (R.check_churn && *(volatile unsigned long long*)&counters[C_CHURN] != 0) return;
@@ -63,13 +62,11 @@ __global__ void __launch_bounds__(THREADS, (1152 / THREADS < 32 ? 1152 / THREADS
   __syncthreads();
 
   unsigned long long tk_next = 0;
-  // warp 0: the ticket thread 0 drew goes into pipeline slot k, with its descriptor
+  // thread 0: the ticket it drew goes into descriptor slot k, with its descriptor
   auto fetch_desc = [&](uint32_t k) {
-    const uint32_t nt = __shfl_sync(0xffffffffu, uint32_t(tk_next), 0);
-    if (lane == 0) {
-      if (nt < R.n_tiles) s_desc[k] = R.tiles[nt];
-      s_tk[k] = nt;
-    }
+    const uint32_t nt = uint32_t(tk_next);
+    if (nt < R.n_tiles) s_desc[k] = R.tiles[nt];
+    s_tk[k] = nt;
   };
   // warp 0: bulk copy of the label text of the tile in slot k into the (single) stage
   auto issue_labels = [&](uint32_t k) {
@@ -83,13 +80,12 @@ __global__ void __launch_bounds__(THREADS, (1152 / THREADS < 32 ? 1152 / THREADS
       } else {
         mbar_arrive(bar);
       }
-      s_l0 = uint32_t(L0 - g0);
     }
   };
 
   // ---- MEASURE the tile in pipeline slot k: value text into slot buffer k, exact line lengths, CTA scan, and the
   // tile's size published for the look-back of its successors.  Contains one CTA barrier.
-  auto measure = [&](uint32_t k, LineState& L) {
+  auto measure = [&](uint32_t k, uint32_t sb, LineState& L) {
     const Tile tile = s_desc[k];
     const uint32_t t = s_tk[k];
     const FamMeta& fm = R.fam[tile.family];
@@ -102,7 +98,7 @@ __global__ void __launch_bounds__(THREADS, (1152 / THREADS < 32 ? 1152 / THREADS
       L.live = live;
       if (live) {
         uint32_t vs;
-        L.vlen = format_slot(v, smem + lay.slots + (k * THREADS + tid) * kSlotBytes, vs);
+        L.vlen = format_slot(v, smem + lay.slots + (sb * THREADS + tid) * kSlotBytes, vs);
         L.vstart = vs - 1;  // the space before the value
         L.len = fm.name_len + L.lbl_len + L.vlen + 2;
       }
@@ -129,12 +125,12 @@ __global__ void __launch_bounds__(THREADS, (1152 / THREADS < 32 ? 1152 / THREADS
   uint32_t parity = 0;
   KGX_PC_DECL;
   // ---- EMIT the tile in pipeline slot k (measured one iteration ago): global offset by look-back, header, lines
-  auto emit = [&](uint32_t k, const LineState& L) {
+  auto emit = [&](uint32_t k, uint32_t sb, const LineState& L, bool more) {
     const Tile tile = s_desc[k];
     const uint32_t t = s_tk[k];
     const FamMeta& fm = R.fam[tile.family];
     const uint32_t name_len = fm.name_len;
-    const uint32_t slot = sm0 + lay.slots + (k * THREADS + tid) * kSlotBytes;
+    const uint32_t slot = sm0 + lay.slots + (sb * THREADS + tid) * kSlotBytes;
     // decoupled look-back, 32 predecessors per step; every warp resolves it for itself (no barrier, no broadcast)
     unsigned long long base = 0;
     if (t > 0) {
@@ -178,12 +174,17 @@ __global__ void __launch_bounds__(THREADS, (1152 / THREADS < 32 ? 1152 / THREADS
     uint8_t* galn = R.out + (base & ~15ull);  // 16-aligned origin: position v lives at galn + v
     const uint32_t sh = uint32_t(base & 15);
     if (L.hdr) for (uint32_t i = tid; i < L.hdr; i += THREADS) gtile[i] = fm.header[i];
+    // The ticket counter's reply takes ~0.5 us under load.  Drawn here — after the look-back, before the lines — it is
+    // back by the time thread 0's line is out, and thread 0 fetches the descriptor before the end-of-tile barrier
+    // (1.381 -> 1.351 ms).  Drawn earlier (before the look-back: 1.374; a whole iteration ahead: 1.59) tiles drift out of
+    // ticket order and every look-back gets longer.
+    if (tid == 0 && more) tk_next = atomicAdd(ticket, 1ull);
     KGX_PC(3);  // look-back
-    mbar_wait(bar, parity);  // the tile's label text has landed (issued during the previous iteration's hand-over)
+    mbar_wait(bar, parity);  // the tile's label text has landed (issued right after the previous end-of-tile barrier)
     parity ^= 1;
     KGX_PC(4);  // header + label wait
     if (L.live) {
-      const uint32_t lbl_src = sm0 + lay.stage + 32 + s_l0 + L.lbl_at;
+      const uint32_t lbl_src = sm0 + lay.stage + 32 + uint32_t(tile.lbl0 & 127ull) + L.lbl_at;
       const uint32_t g = sh + L.off;                                                  // first byte of my line (position)
       const uint32_t b0 = g + name_len, b1 = b0 + L.lbl_len, b2 = b1 + L.vlen + 2;    // source boundaries; b2 = line end
       const uint32_t start = (g + 15u) & ~15u;
@@ -230,42 +231,38 @@ __global__ void __launch_bounds__(THREADS, (1152 / THREADS < 32 ? 1152 / THREADS
         for (uint32_t q = 0; q < e; ++q) galn[p + q] = sp[q];
       }
     }
+    if (tid == 0 && more) fetch_desc((k + 2) % 3);  // nobody reads that slot before the end-of-tile barrier
   };
 
   // ---- prologue: first tile measured, second ticket drawn
-  if (tid == 0) tk_next = atomicAdd(ticket, 1ull);
-  if (wid == 0) { fetch_desc(0); __syncwarp(); if (s_tk[0] < R.n_tiles) issue_labels(0); }
+  if (tid == 0) { tk_next = atomicAdd(ticket, 1ull); fetch_desc(0); }
   __syncthreads();
   if (s_tk[0] >= R.n_tiles) return;
+  if (wid == 0) issue_labels(0);
   LineState cur, nxt;
-  measure(0, cur);
-  if (tid == 0) tk_next = atomicAdd(ticket, 1ull);
-  if (wid == 0) fetch_desc(1);
+  measure(0, 0, cur);
+  if (tid == 0) { tk_next = atomicAdd(ticket, 1ull); fetch_desc(1); }
   __syncthreads();
 
-  uint32_t b = 0;
+  uint32_t d = 0, sb = 0;  // descriptor slot and value-slot buffer of the tile being emitted
   for (;;) {
-    const bool more = s_tk[b ^ 1] < R.n_tiles;  // CTA-uniform
-    if (more) measure(b ^ 1, nxt);
+    const uint32_t d1 = d == 2 ? 0 : d + 1;
+    const bool more = s_tk[d1] < R.n_tiles;  // CTA-uniform
+    if (more) measure(d1, sb ^ 1, nxt);
     KGX_PC(1);  // measure the next tile (state loads + format + scan)
-    emit(b, cur);
-    KGX_PC(5);  // stream my line
-    // the ticket counter's reply takes ~0.5 us under load: drawn as soon as thread 0's own line is out.  (Drawing it a
-    // whole iteration ahead, descriptor loaded between MEASURE and EMIT, hides that latency but lets tiles drift out
-    // of ticket order: 1.42 -> 1.59 ms, profiles/README.md round 2.)
-    if (tid == 0 && more) tk_next = atomicAdd(ticket, 1ull);
-    __syncthreads();  // label stage and slot buffer b are free
+    emit(d, sb, cur, more);
+    KGX_PC(5);  // stream my line (+ thread 0: descriptor of the tile after next)
+    __syncthreads();  // label stage and slot buffer sb are free; the new descriptor is visible
     KGX_PC(6);  // end-of-tile barrier
     if (!more) { KGX_PC_FLUSH; return; }
-    if (wid == 0) { issue_labels(b ^ 1); fetch_desc(b); }  // labels of the measured tile; ticket + descriptor of the one after
-    KGX_PC(7);  // ticket + descriptor
-    __syncthreads();  // s_tk / s_desc / s_l0 visible
-    KGX_PC(8);
+    if (wid == 0) issue_labels(d1);  // labels of the measured tile
+    KGX_PC(7);
 #ifdef KGX_PHASE_CLOCKS
     ++pc_tiles;
 #endif
     cur = nxt;
-    b ^= 1;
+    d = d1;
+    sb ^= 1;
   }
 }
 

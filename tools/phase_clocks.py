@@ -11,8 +11,8 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SO = os.path.join(ROOT, "tools", "exp", "libkgx_phase.so")
-PHASES = ["state loads", "format", "scan barrier", "look-back", "header+label wait", "stream line", "end barrier",
-          "ticket+descriptor", "hand-over barrier"]
+PHASES = ["-", "measure next tile", "-", "look-back", "header+label wait", "stream line (+descriptor)", "end barrier",
+          "label copy issue", "-"]
 
 if __name__ == "__main__":
     sys.path.insert(0, ROOT)
