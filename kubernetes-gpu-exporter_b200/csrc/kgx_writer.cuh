@@ -61,10 +61,12 @@ __device__ __forceinline__ uint4 merge16(uint4 lo, uint4 hi, uint32_t e) {
 __device__ unsigned long long g_phase_clk[16];
 #define KGX_PC_DECL unsigned long long pc_acc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; long long pc_t = clock64(); unsigned long long pc_tiles = 0
 #define KGX_PC(i) do { if (tid == 0) { const long long n_ = clock64(); pc_acc[i] += (unsigned long long)(n_ - pc_t); pc_t = n_; } } while (0)
+#define KGX_PC_COUNT(i) do { if (tid == 0) pc_acc[i] += 1; } while (0)
 #define KGX_PC_FLUSH do { if (tid == 0) { for (int i_ = 0; i_ < 10; ++i_) atomicAdd(&g_phase_clk[i_], pc_acc[i_]); atomicAdd(&g_phase_clk[10], pc_tiles); } } while (0)
 #else
 #define KGX_PC_DECL
 #define KGX_PC(i)
+#define KGX_PC_COUNT(i)
 #define KGX_PC_FLUSH
 #endif
 

@@ -151,7 +151,7 @@ __global__ void __launch_bounds__(THREADS, (1152 / THREADS < 32 ? 1152 / THREADS
 #pragma unroll
         for (int q = 0; q < kLookBack5; ++q) {
           const long long at = p - 32 * q;
-          while (!st_published(st[q], R.epoch)) st[q] = *(volatile unsigned long long*)&R.tile_state[at];
+          while (!st_published(st[q], R.epoch)) { st[q] = *(volatile unsigned long long*)&R.tile_state[at]; KGX_PC_COUNT(9); }
           const uint32_t pfx = __ballot_sync(0xffffffffu, (st[q] & kStMask) == kStPrefix);
           if (!found) {  // warp-uniform
             const uint32_t first = pfx ? uint32_t(__ffs(pfx) - 1) : 32u;
@@ -161,6 +161,7 @@ __global__ void __launch_bounds__(THREADS, (1152 / THREADS < 32 ? 1152 / THREADS
         }
         for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
         base += v;
+        KGX_PC_COUNT(8);
         if (found) break;
         p -= 32 * kLookBack5;
       }

@@ -53,7 +53,8 @@ if __name__ == "__main__":
     prof = g.profile()
     tiles = out[10]
     print("render %.4f ms/launch, %d tiles/launch" % (prof["render"][0] / K, tiles // K))
-    tot = sum(out[i] for i in range(9))
-    for i, name in enumerate(PHASES):
+    tot = sum(out[i] for i in range(8))
+    for i, name in enumerate(PHASES[:8]):
         print("%-20s %8.0f cycles/tile  %5.1f %%" % (name, out[i] / tiles, 100.0 * out[i] / tot))
     print("%-20s %8.0f cycles/tile" % ("total", tot / tiles))
+    print("look-back: %.2f steps of 32 predecessors per tile, %.2f re-polls of an unpublished word per tile (thread 0)" % (out[8] / tiles, out[9] / tiles))
