@@ -187,6 +187,23 @@ def test_multi_node_fleet(kgo, mode, shuffle):
     _same(g, o)
 
 
+@pytest.mark.parametrize("mode", [MODE_R_INTENDED, MODE_X])
+def test_every_depth_of_the_writer_pipeline(kgo, mode):
+    """The writer keeps three tiles in flight (emitted, measured, descriptor fetched): one to a dozen 128-line tiles per
+    launch, series counts on and around the tile size, on one node and on three."""
+    for nodes, procs in [(1, 1), (1, 2), (1, 127), (1, 128), (1, 129), (1, 255), (1, 256), (1, 257), (1, 385), (1, 640),
+                         (3, 1), (3, 128), (3, 129), (3, 300)]:
+        f = Fleet(n_nodes=nodes, pods=max(1, procs // 2), procs=procs, seed=0xB200 + 77 + procs)
+        t = f.table(mode)
+        g, o = _pair(kgo, mode)
+        g.set_table(t); o.set_table(t)
+        s = f.scrape(0)
+        g.ingest(s); o.ingest(s)
+        _same(g, o)
+        _same(g, o)  # a second launch: the other ticket, the next epoch
+        g.close()
+
+
 def test_x_window_of_scrapes_and_reset(kgo):
     f = Fleet(n_nodes=4, pods=64, procs=512, seed=0xB200 + 5, scrapes=6)
     t = f.table(MODE_X)
