@@ -411,7 +411,7 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from kgx_b200 import kgx
+    from kgx_b200 import fleetshard, kgx
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -421,6 +421,7 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        fleetshard.nccl_gather_env()
         dist.init_process_group("nccl", device_id=dev)
 
     fleet, table, cols = build_fleet(rank, args.nodes)

@@ -23,6 +23,7 @@ def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    fleetshard.nccl_gather_env()
     dist.init_process_group("nccl", device_id=dev)
     ok = True
     for cfg, mode, n_total in ((3, MODE_R_INTENDED, 128), (4, MODE_X, 96)):
