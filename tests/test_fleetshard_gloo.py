@@ -82,3 +82,13 @@ def test_node_range_partitions():
             assert all(parts[i][1] == parts[i + 1][0] for i in range(w - 1))
             sizes = [b - a for a, b in parts]
             assert max(sizes) - min(sizes) <= 1
+
+
+def test_nccl_gather_env_sets_defaults_and_respects_the_environment(monkeypatch):
+    from kgx_b200 import fleetshard
+    for k in ("NCCL_MIN_P2P_NCHANNELS", "NCCL_MAX_P2P_NCHANNELS", "NCCL_MAX_NCHANNELS"):
+        monkeypatch.delenv(k, raising=False)
+    monkeypatch.setenv("NCCL_MAX_NCHANNELS", "16")      # the operator's choice wins
+    fleetshard.nccl_gather_env()
+    assert os.environ["NCCL_MIN_P2P_NCHANNELS"] == "64" and os.environ["NCCL_MAX_P2P_NCHANNELS"] == "64"
+    assert os.environ["NCCL_MAX_NCHANNELS"] == "16"
