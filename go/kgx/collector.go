@@ -134,6 +134,9 @@ func Handler(ctx *Ctx, fallback http.Handler) http.Handler {
 // scrape waits.
 func StreamingHandler(ctx *Ctx, fallback http.Handler, chunkBytes int) http.Handler {
 	var mu sync.Mutex
+	if chunkBytes <= 0 {
+		chunkBytes = 8 << 20
+	}
 	chunk := make([]byte, chunkBytes)
 	return http.HandlerFunc(func(w http.ResponseWriter, r *http.Request) {
 		ct := expfmt.Negotiate(r.Header)

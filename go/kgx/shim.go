@@ -220,6 +220,9 @@ func (c *Ctx) RenderDevice() (int, error) {
 // whatever the size of the body, and the first bytes leave one render and one
 // chunk copy after the call.  The caller serialises scrapes on this Ctx.
 func (c *Ctx) WriteBodyTo(w io.Writer, chunk []byte) (int64, error) {
+	if len(chunk) == 0 {
+		chunk = make([]byte, 1<<20)
+	}
 	if _, err := c.RenderDevice(); err != nil {
 		return 0, err
 	}
