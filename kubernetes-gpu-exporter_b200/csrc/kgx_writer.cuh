@@ -45,6 +45,19 @@ __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
 __device__ __forceinline__ void stg128_cs(uint8_t* p, uint4 v) {
   asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
+// The chunk `hi` at `p` (16-byte aligned): if `pair`, stored together with `lo` as the 32 bytes at p - 16 (32-byte
+// aligned; sm_100: STG.256); if `single`, stored alone; else nothing.  Predicated, no branch.
+__device__ __forceinline__ void st_pair_or_single(uint8_t* p, const uint4& lo, const uint4& hi, bool pair, bool single) {
+  asm volatile(
+      "{\n\t.reg .pred q, s;\n\t.reg .u64 a;\n\t"
+      "setp.ne.u32 q, %9, 0;\n\t"
+      "setp.ne.u32 s, %10, 0;\n\t"
+      "sub.u64 a, %0, 16;\n\t"
+      "@q st.global.cs.v8.b32 [a], {%1, %2, %3, %4, %5, %6, %7, %8};\n\t"
+      "@s st.global.cs.v4.b32 [%0], {%5, %6, %7, %8};\n\t}" ::"l"(p),
+      "r"(lo.x), "r"(lo.y), "r"(lo.z), "r"(lo.w), "r"(hi.x), "r"(hi.y), "r"(hi.z), "r"(hi.w), "r"(uint32_t(pair)), "r"(uint32_t(single))
+      : "memory");
+}
 // bytes [0,e) from lo, bytes [e,16) from hi (0 < e < 16).  The masks are computed:
 // the writer is bound by the L1/LSU data pipe, not by the ALU.
 __device__ __forceinline__ uint4 merge16(uint4 lo, uint4 hi, uint32_t e) {

@@ -172,8 +172,11 @@ __global__ void __launch_bounds__(THREADS, (1152 / THREADS < 32 ? 1152 / THREADS
       if (t == R.n_tiles - 1) { counters[C_TOTAL_LEN] = base + L.total; if (R.host_len) *R.host_len = base + L.total; }
     }
     uint8_t* gtile = R.out + base;            // first byte of the tile in the output
-    uint8_t* galn = R.out + (base & ~15ull);  // 16-aligned origin: position v lives at galn + v
-    const uint32_t sh = uint32_t(base & 15);
+    // 32-byte aligned origin: position v lives at galn + v.  Chunks are 16 bytes; two that fill a 32-byte sector
+    // leave in one 256-bit store.
+    const unsigned long long gabs = reinterpret_cast<unsigned long long>(R.out) + base;
+    uint8_t* galn = reinterpret_cast<uint8_t*>(gabs & ~31ull);
+    const uint32_t sh = uint32_t(gabs & 31);
     if (L.hdr) for (uint32_t i = tid; i < L.hdr; i += THREADS) gtile[i] = fm.header[i];
     // The ticket counter's reply takes ~0.5 us under load.  Drawn here — after the look-back, before the lines — it is
     // back by the time thread 0's line is out, and thread 0 fetches the descriptor before the end-of-tile barrier
@@ -197,6 +200,16 @@ __global__ void __launch_bounds__(THREADS, (1152 / THREADS < 32 ? 1152 / THREADS
       }
       uint32_t p = start, e = 0;  // `a4` holds the chunk at p, of which the first `e` bytes are already final
       uint4 a4 = make_uint4(0, 0, 0, 0);
+      // A 16-byte store is half a 32-byte sector on its way to L2, and the stream of partial sectors is what the writer
+      // waits for.  So a finished chunk in the lower half of a sector waits in `lo4` for its upper neighbour and the
+      // two leave in one 256-bit store.  Straight-line code: the stores are predicated, the pending half is a select.
+      uint4 lo4 = make_uint4(0, 0, 0, 0);
+      auto put = [&](const uint4& c) {  // the finished chunk at position p
+        const uint32_t odd = p & 16u;
+        st_pair_or_single(galn + p, lo4, c, odd != 0 && p > start, odd != 0 && p == start);
+        lo4.x = odd ? lo4.x : c.x; lo4.y = odd ? lo4.y : c.y; lo4.z = odd ? lo4.z : c.z; lo4.w = odd ? lo4.w : c.w;
+        p += 16;
+      };
       auto append = [&](uint32_t d, uint32_t b) {  // source = position + d, up to position b (exclusive)
         uint32_t wa = (p + d) & ~3u;
         const uint32_t r = ((p + d) & 3u) * 8u;
@@ -209,12 +222,10 @@ __global__ void __launch_bounds__(THREADS, (1152 / THREADS < 32 ? 1152 / THREADS
         const uint4 nw = chunk();
         a4 = e ? merge16(a4, nw, e) : nw;
         if (b >= p + 16) {
-          stg128_cs(galn + p, a4);
-          p += 16;
+          put(a4);
           step();
           while (p + 16 <= b) {
-            stg128_cs(galn + p, chunk());
-            p += 16;
+            put(chunk());
             step();
           }
           a4 = chunk();
@@ -224,9 +235,9 @@ __global__ void __launch_bounds__(THREADS, (1152 / THREADS < 32 ? 1152 / THREADS
       append(d0, b0);  // metric name
       append(d1, b1);  // labels
       append(d2, b2);  // " <value>\n"
-      if (!L.last_live) {
-        append(d3, stop);  // the head of the next line's name completes my last chunk
-      } else if (e) {      // the tile ends inside a chunk: its bytes belong to me, the rest to the next tile
+      if (!L.last_live) append(d3, stop);  // the head of the next line's name completes my last chunk
+      if ((p & 16u) && p > start) stg128_cs(galn + p - 16, lo4);  // a lower half whose neighbour is not mine
+      if (L.last_live && e) {      // the tile ends inside a chunk: its bytes belong to me, the rest to the next tile
         s_tail = a4;
         const uint8_t* sp = reinterpret_cast<const uint8_t*>(&s_tail);
         for (uint32_t q = 0; q < e; ++q) galn[p + q] = sp[q];
