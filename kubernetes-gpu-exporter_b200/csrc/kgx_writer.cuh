@@ -12,7 +12,8 @@
 //     never waits on one that has not started;
 //   * each thread then streams its line to the output as 16-byte chunks aligned to the GLOBAL address: a chunk belongs
 //     to the line that holds its first byte, so no two lanes ever write the same chunk and every store is a full
-//     streaming STG.128.  The four sources of a line (metric name, staged labels, value slot, head of the next line's
+//     chunk — or two: chunks that fill one 32-byte sector leave together as STG.256 (a 16-byte store is half a sector
+//     on its way to L2).  The four sources of a line (metric name, staged labels, value slot, head of the next line's
 //     name) are appended one after the other, all lanes of a warp in the same source at the same time; word loads +
 //     funnel shifts realign, computed byte masks merge the one chunk that straddles two sources.  Only the head of a
 //     tile's first line and the tail of its last one are partial chunks: those few bytes are byte stores.
